@@ -1,0 +1,71 @@
+// TEST HARNESS: compiles the product's device headers for the host (VG_HOST_EMU) so the field, curve,
+// hash and walk logic can be checked against the oracle on a machine without a GPU.
+// Not part of the product; never used on the GPU path.
+#define VG_HOST_EMU 1
+#include <vector>
+#include <cstring>
+#include "../../vgen_b200/csrc/match.cuh"
+
+static const uint32_t G_XY[16] = {
+    0x16F81798, 0x59F2815B, 0x2DCE28D9, 0x029BFCDB, 0xCE870B07, 0x55A06295, 0xF9DCBBAC, 0x79BE667E,
+    0xFB10D4B8, 0x9C47D08F, 0xA6855419, 0xFD17B448, 0x0E1108A8, 0x5DA4FBFC, 0x26A3C465, 0x483ADA77};
+static std::vector<uint32_t> g_pow2;
+static void ensure_pow2() { if (g_pow2.empty()) { g_pow2.resize(256 * 16); vg_build_pow2(g_pow2.data(), G_XY); } }
+
+extern "C" {
+void emu_fe_mul(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_mul(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }
+void emu_fe_add(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_add(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }
+void emu_fe_sub(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_sub(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }
+void emu_fe_inv(const uint32_t *a, uint32_t *r) { fe x, z; memcpy(x.v, a, 32); fe_inv(z, x); fe_canon(z); memcpy(r, z.v, 32); }
+int emu_scalar_mul(const uint32_t *k, uint32_t *x, uint32_t *y) {
+    ensure_pow2(); fe fx, fy; bool ok = scalar_is_valid(k) && scalar_mul_pow2(fx, fy, k, g_pow2.data());
+    memcpy(x, fx.v, 32); memcpy(y, fy.v, 32); return ok ? 0 : -1;
+}
+void emu_digest(int fmt, const uint32_t *x, const uint32_t *y, uint32_t *dg) {
+    fe fx, fy; memcpy(fx.v, x, 32); memcpy(fy.v, y, 32);
+    switch (fmt) {
+        case 0: vg_digest_of_point<0>(dg, fx, fy); break; case 1: vg_digest_of_point<1>(dg, fx, fy); break;
+        case 2: vg_digest_of_point<2>(dg, fx, fy); break; case 3: vg_digest_of_point<3>(dg, fx, fy); break;
+        case 4: vg_digest_of_point<4>(dg, fx, fy); break; default: vg_digest_of_point<5>(dg, fx, fy); break;
+    }
+}
+void emu_keccak_hex40(const uint32_t *m, uint32_t *out) { keccak_hex40(out, m); }
+
+// Walk n_windows windows of T threads x 2H keys from scalar `start`, dumping `stride` digest bytes per key.
+// Returns the number of degenerate thread-batches seen.
+int emu_walk_dump(int fmt, const uint32_t *start, uint32_t T, uint32_t H, uint32_t n_windows, uint32_t stride, uint8_t *out) {
+    ensure_pow2();
+    const uint64_t B = 2ull * H, W = (uint64_t)T * B;
+    std::vector<uint32_t> gtab(H * 16), centers(16 * T), scratch((size_t)(H + 1) * 8 * T), colbuf(16);
+    for (uint32_t i = 0; i < H; i++) {
+        uint32_t k[8] = {i + 1, 0, 0, 0, 0, 0, 0, 0};
+        vg_point_of_scalar(colbuf.data(), 1, 0, k, g_pow2.data());
+        memcpy(&gtab[i * 16], colbuf.data(), 64);
+    }
+    vg_scan_params P; memset(&P, 0, sizeof P);
+    uint32_t wk[8] = {(uint32_t)W, (uint32_t)(W >> 32), 0, 0, 0, 0, 0, 0};
+    vg_point_of_scalar(colbuf.data(), 1, 0, wk, g_pow2.data());
+    memcpy(P.stride_pt, colbuf.data(), 64);
+    for (uint32_t t = 0; t < T; t++) {
+        uint32_t k[8]; scalar_add_u64(k, start, (uint64_t)t * B + H);
+        vg_point_of_scalar(centers.data(), T, t, k, g_pow2.data());
+    }
+    uint32_t hitc = 0, degc = 0; std::vector<uint32_t> degl(T);
+    P.n_threads = T; P.half = H; P.centers = centers.data(); P.scratch = scratch.data(); P.gtab = gtab.data();
+    P.limit = W; P.hit_count = &hitc; P.degen_count = &degc; P.degen_list = degl.data(); P.degen_cap = T;
+    P.dump_stride = stride;
+    for (uint32_t w = 0; w < n_windows; w++) {
+        P.dump = out + (size_t)w * W * stride;
+        for (uint32_t t = 0; t < T; t++) {
+            switch (fmt) {
+                case 0: vg_walk_thread<0, VG_MODE_DUMP>(P, gtab.data(), t); break;
+                case 1: vg_walk_thread<1, VG_MODE_DUMP>(P, gtab.data(), t); break;
+                case 3: vg_walk_thread<3, VG_MODE_DUMP>(P, gtab.data(), t); break;
+                case 4: vg_walk_thread<4, VG_MODE_DUMP>(P, gtab.data(), t); break;
+                default: vg_walk_thread<5, VG_MODE_DUMP>(P, gtab.data(), t); break;
+            }
+        }
+    }
+    return (int)degc;
+}
+}

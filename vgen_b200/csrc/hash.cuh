@@ -1,0 +1,242 @@
+// Register-resident single-message hashes for the scan kernels: SHA-256 (33/65/22/21/32-byte
+// messages), RIPEMD-160 (32-byte message), Keccak-256 (64- and 40-byte messages).
+//
+// Replaces src/shaders/sha256.wgsl:43-170 and src/shaders/ripemd160.wgsl:10-100 (one-block
+// versions with the padding baked in) and adds what the reference left on the host: the second
+// hash160 of P2SH-P2WPKH (src/gpu.rs:1051-1060), the uncompressed-key hash
+// (src/address.rs:121-124) and Keccak-256 (src/address.rs:95-113,176-198).
+// All loops are fully unrolled; message words that are padding constants fold at compile time.
+#pragma once
+#include <stdint.h>
+#include "fe.cuh"
+
+#ifdef VG_HOST_EMU
+static inline uint32_t vg_rotr(uint32_t x, int n) { return (x >> n) | (x << (32 - n)); }
+static inline uint32_t vg_rotl(uint32_t x, int n) { return (x << n) | (x >> (32 - n)); }
+static inline uint32_t vg_bswap(uint32_t x) { return __builtin_bswap32(x); }
+static inline uint32_t vg_shf_l(uint32_t lo, uint32_t hi, int n) { return (hi << n) | (lo >> (32 - n)); }  // 0<n<32
+#define VG_CONST static const
+#else
+__device__ __forceinline__ uint32_t vg_rotr(uint32_t x, int n) { return __funnelshift_r(x, x, n); }
+__device__ __forceinline__ uint32_t vg_rotl(uint32_t x, int n) { return __funnelshift_l(x, x, n); }
+__device__ __forceinline__ uint32_t vg_bswap(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
+__device__ __forceinline__ uint32_t vg_shf_l(uint32_t lo, uint32_t hi, int n) { return __funnelshift_l(lo, hi, n); }
+#define VG_CONST __device__ __constant__ const
+#endif
+
+VG_CONST uint32_t VG_SHA_K[64] = {
+    0x428a2f98,0x71374491,0xb5c0fbcf,0xe9b5dba5,0x3956c25b,0x59f111f1,0x923f82a4,0xab1c5ed5,
+    0xd807aa98,0x12835b01,0x243185be,0x550c7dc3,0x72be5d74,0x80deb1fe,0x9bdc06a7,0xc19bf174,
+    0xe49b69c1,0xefbe4786,0x0fc19dc6,0x240ca1cc,0x2de92c6f,0x4a7484aa,0x5cb0a9dc,0x76f988da,
+    0x983e5152,0xa831c66d,0xb00327c8,0xbf597fc7,0xc6e00bf3,0xd5a79147,0x06ca6351,0x14292967,
+    0x27b70a85,0x2e1b2138,0x4d2c6dfc,0x53380d13,0x650a7354,0x766a0abb,0x81c2c92e,0x92722c85,
+    0xa2bfe8a1,0xa81a664b,0xc24b8b70,0xc76c51a3,0xd192e819,0xd6990624,0xf40e3585,0x106aa070,
+    0x19a4c116,0x1e376c08,0x2748774c,0x34b0bcb5,0x391c0cb3,0x4ed8aa4a,0x5b9cca4f,0x682e6ff3,
+    0x748f82ee,0x78a5636f,0x84c87814,0x8cc70208,0x90befffa,0xa4506ceb,0xbef9a3f7,0xc67178f2};
+
+#define VG_SHA_IV {0x6a09e667u,0xbb67ae85u,0x3c6ef372u,0xa54ff53au,0x510e527fu,0x9b05688cu,0x1f83d9abu,0x5be0cd19u}
+
+// one compression; w[] is consumed as the rolling schedule
+VG_DEV void sha256_compress(uint32_t st[8], uint32_t w[16]) {
+    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+    VG_UNROLL for (int i = 0; i < 64; i++) {
+        if (i >= 16) {
+            uint32_t w15 = w[(i - 15) & 15], w2 = w[(i - 2) & 15];
+            uint32_t s0 = vg_rotr(w15, 7) ^ vg_rotr(w15, 18) ^ (w15 >> 3);
+            uint32_t s1 = vg_rotr(w2, 17) ^ vg_rotr(w2, 19) ^ (w2 >> 10);
+            w[i & 15] = w[i & 15] + s0 + w[(i - 7) & 15] + s1;
+        }
+        uint32_t S1 = vg_rotr(e, 6) ^ vg_rotr(e, 11) ^ vg_rotr(e, 25);
+        uint32_t ch = (e & f) ^ (~e & g);
+        uint32_t t1 = h + S1 + ch + VG_SHA_K[i] + w[i & 15];
+        uint32_t S0 = vg_rotr(a, 2) ^ vg_rotr(a, 13) ^ vg_rotr(a, 22);
+        uint32_t mj = (a & b) | (c & (a | b));
+        h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + S0 + mj;
+    }
+    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+}
+// SHA-256(prefix || X) for a 33-byte compressed key; x is a canonical field element
+VG_DEV void sha256_pub33(uint32_t out[8], uint32_t prefix, const fe &x) {
+    uint32_t w[16];
+    w[0] = (prefix << 24) | (x.v[7] >> 8);
+    VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(x.v[7 - k], x.v[8 - k], 24);
+    w[8] = (x.v[0] << 24) | 0x00800000u;
+    VG_UNROLL for (int k = 9; k < 15; k++) w[k] = 0;
+    w[15] = 33 * 8;
+    uint32_t st[8] = VG_SHA_IV;
+    sha256_compress(st, w);
+    VG_UNROLL for (int i = 0; i < 8; i++) out[i] = st[i];
+}
+// SHA-256(04 || X || Y) for a 65-byte uncompressed key (two blocks)
+VG_DEV void sha256_pub65(uint32_t out[8], const fe &x, const fe &y) {
+    uint32_t w[16];
+    w[0] = (4u << 24) | (x.v[7] >> 8);
+    VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(x.v[7 - k], x.v[8 - k], 24);
+    w[8] = (x.v[0] << 24) | (y.v[7] >> 8);
+    VG_UNROLL for (int k = 1; k < 8; k++) w[8 + k] = vg_shf_l(y.v[7 - k], y.v[8 - k], 24);
+    uint32_t st[8] = VG_SHA_IV;
+    sha256_compress(st, w);
+    w[0] = (y.v[0] << 24) | 0x00800000u;
+    VG_UNROLL for (int k = 1; k < 15; k++) w[k] = 0;
+    w[15] = 65 * 8;
+    sha256_compress(st, w);
+    VG_UNROLL for (int i = 0; i < 8; i++) out[i] = st[i];
+}
+// SHA-256 of a message of nbytes (<= 55) given as big-endian words (unused tail bytes must be 0)
+VG_DEV void sha256_short(uint32_t out[8], const uint32_t *m, int nbytes) {
+    uint32_t w[16];
+    VG_UNROLL for (int k = 0; k < 15; k++) w[k] = (k * 4 < nbytes + 1) ? m[k] : 0u;
+    w[nbytes >> 2] |= 0x80u << (24 - 8 * (nbytes & 3));
+    w[15] = (uint32_t)nbytes * 8;
+    uint32_t st[8] = VG_SHA_IV;
+    sha256_compress(st, w);
+    VG_UNROLL for (int i = 0; i < 8; i++) out[i] = st[i];
+}
+
+// ---- RIPEMD-160 of a 32-byte message given as 8 big-endian SHA words ----
+#define VG_RMD_F0(x, y, z) ((x) ^ (y) ^ (z))
+#define VG_RMD_F1(x, y, z) (((x) & (y)) | (~(x) & (z)))
+#define VG_RMD_F2(x, y, z) (((x) | ~(y)) ^ (z))
+#define VG_RMD_F3(x, y, z) (((x) & (z)) | ((y) & ~(z)))
+#define VG_RMD_F4(x, y, z) ((x) ^ ((y) | ~(z)))
+#define VG_RMD_STEP(F, a, b, c, d, e, xw, k, s) \
+    a = vg_rotl(a + F(b, c, d) + (xw) + (k), s) + e; c = vg_rotl(c, 10);
+
+VG_DEV void ripemd160_32(uint32_t out[5], const uint32_t sha[8]) {
+    uint32_t x[16];
+    VG_UNROLL for (int i = 0; i < 8; i++) x[i] = vg_bswap(sha[i]);
+    x[8] = 0x80u; x[9] = 0; x[10] = 0; x[11] = 0; x[12] = 0; x[13] = 0; x[14] = 256u; x[15] = 0;
+    const uint32_t h0 = 0x67452301u, h1 = 0xEFCDAB89u, h2 = 0x98BADCFEu, h3 = 0x10325476u, h4 = 0xC3D2E1F0u;
+    uint32_t a = h0, b = h1, c = h2, d = h3, e = h4, A = h0, B = h1, C = h2, D = h3, E = h4;
+#define L(F, a, b, c, d, e, r, s, k) VG_RMD_STEP(F, a, b, c, d, e, x[r], k, s)
+    // left line
+    L(VG_RMD_F0,a,b,c,d,e,0,11,0u) L(VG_RMD_F0,e,a,b,c,d,1,14,0u) L(VG_RMD_F0,d,e,a,b,c,2,15,0u) L(VG_RMD_F0,c,d,e,a,b,3,12,0u)
+    L(VG_RMD_F0,b,c,d,e,a,4,5,0u) L(VG_RMD_F0,a,b,c,d,e,5,8,0u) L(VG_RMD_F0,e,a,b,c,d,6,7,0u) L(VG_RMD_F0,d,e,a,b,c,7,9,0u)
+    L(VG_RMD_F0,c,d,e,a,b,8,11,0u) L(VG_RMD_F0,b,c,d,e,a,9,13,0u) L(VG_RMD_F0,a,b,c,d,e,10,14,0u) L(VG_RMD_F0,e,a,b,c,d,11,15,0u)
+    L(VG_RMD_F0,d,e,a,b,c,12,6,0u) L(VG_RMD_F0,c,d,e,a,b,13,7,0u) L(VG_RMD_F0,b,c,d,e,a,14,9,0u) L(VG_RMD_F0,a,b,c,d,e,15,8,0u)
+#define K1 0x5A827999u
+    L(VG_RMD_F1,e,a,b,c,d,7,7,K1) L(VG_RMD_F1,d,e,a,b,c,4,6,K1) L(VG_RMD_F1,c,d,e,a,b,13,8,K1) L(VG_RMD_F1,b,c,d,e,a,1,13,K1)
+    L(VG_RMD_F1,a,b,c,d,e,10,11,K1) L(VG_RMD_F1,e,a,b,c,d,6,9,K1) L(VG_RMD_F1,d,e,a,b,c,15,7,K1) L(VG_RMD_F1,c,d,e,a,b,3,15,K1)
+    L(VG_RMD_F1,b,c,d,e,a,12,7,K1) L(VG_RMD_F1,a,b,c,d,e,0,12,K1) L(VG_RMD_F1,e,a,b,c,d,9,15,K1) L(VG_RMD_F1,d,e,a,b,c,5,9,K1)
+    L(VG_RMD_F1,c,d,e,a,b,2,11,K1) L(VG_RMD_F1,b,c,d,e,a,14,7,K1) L(VG_RMD_F1,a,b,c,d,e,11,13,K1) L(VG_RMD_F1,e,a,b,c,d,8,12,K1)
+#define K2 0x6ED9EBA1u
+    L(VG_RMD_F2,d,e,a,b,c,3,11,K2) L(VG_RMD_F2,c,d,e,a,b,10,13,K2) L(VG_RMD_F2,b,c,d,e,a,14,6,K2) L(VG_RMD_F2,a,b,c,d,e,4,7,K2)
+    L(VG_RMD_F2,e,a,b,c,d,9,14,K2) L(VG_RMD_F2,d,e,a,b,c,15,9,K2) L(VG_RMD_F2,c,d,e,a,b,8,13,K2) L(VG_RMD_F2,b,c,d,e,a,1,15,K2)
+    L(VG_RMD_F2,a,b,c,d,e,2,14,K2) L(VG_RMD_F2,e,a,b,c,d,7,8,K2) L(VG_RMD_F2,d,e,a,b,c,0,13,K2) L(VG_RMD_F2,c,d,e,a,b,6,6,K2)
+    L(VG_RMD_F2,b,c,d,e,a,13,5,K2) L(VG_RMD_F2,a,b,c,d,e,11,12,K2) L(VG_RMD_F2,e,a,b,c,d,5,7,K2) L(VG_RMD_F2,d,e,a,b,c,12,5,K2)
+#define K3 0x8F1BBCDCu
+    L(VG_RMD_F3,c,d,e,a,b,1,11,K3) L(VG_RMD_F3,b,c,d,e,a,9,12,K3) L(VG_RMD_F3,a,b,c,d,e,11,14,K3) L(VG_RMD_F3,e,a,b,c,d,10,15,K3)
+    L(VG_RMD_F3,d,e,a,b,c,0,14,K3) L(VG_RMD_F3,c,d,e,a,b,8,15,K3) L(VG_RMD_F3,b,c,d,e,a,12,9,K3) L(VG_RMD_F3,a,b,c,d,e,4,8,K3)
+    L(VG_RMD_F3,e,a,b,c,d,13,9,K3) L(VG_RMD_F3,d,e,a,b,c,3,14,K3) L(VG_RMD_F3,c,d,e,a,b,7,5,K3) L(VG_RMD_F3,b,c,d,e,a,15,6,K3)
+    L(VG_RMD_F3,a,b,c,d,e,14,8,K3) L(VG_RMD_F3,e,a,b,c,d,5,6,K3) L(VG_RMD_F3,d,e,a,b,c,6,5,K3) L(VG_RMD_F3,c,d,e,a,b,2,12,K3)
+#define K4 0xA953FD4Eu
+    L(VG_RMD_F4,b,c,d,e,a,4,9,K4) L(VG_RMD_F4,a,b,c,d,e,0,15,K4) L(VG_RMD_F4,e,a,b,c,d,5,5,K4) L(VG_RMD_F4,d,e,a,b,c,9,11,K4)
+    L(VG_RMD_F4,c,d,e,a,b,7,6,K4) L(VG_RMD_F4,b,c,d,e,a,12,8,K4) L(VG_RMD_F4,a,b,c,d,e,2,13,K4) L(VG_RMD_F4,e,a,b,c,d,10,12,K4)
+    L(VG_RMD_F4,d,e,a,b,c,14,5,K4) L(VG_RMD_F4,c,d,e,a,b,1,12,K4) L(VG_RMD_F4,b,c,d,e,a,3,13,K4) L(VG_RMD_F4,a,b,c,d,e,8,14,K4)
+    L(VG_RMD_F4,e,a,b,c,d,11,11,K4) L(VG_RMD_F4,d,e,a,b,c,6,8,K4) L(VG_RMD_F4,c,d,e,a,b,15,5,K4) L(VG_RMD_F4,b,c,d,e,a,13,6,K4)
+    // right line
+#define J0 0x50A28BE6u
+    L(VG_RMD_F4,A,B,C,D,E,5,8,J0) L(VG_RMD_F4,E,A,B,C,D,14,9,J0) L(VG_RMD_F4,D,E,A,B,C,7,9,J0) L(VG_RMD_F4,C,D,E,A,B,0,11,J0)
+    L(VG_RMD_F4,B,C,D,E,A,9,13,J0) L(VG_RMD_F4,A,B,C,D,E,2,15,J0) L(VG_RMD_F4,E,A,B,C,D,11,15,J0) L(VG_RMD_F4,D,E,A,B,C,4,5,J0)
+    L(VG_RMD_F4,C,D,E,A,B,13,7,J0) L(VG_RMD_F4,B,C,D,E,A,6,7,J0) L(VG_RMD_F4,A,B,C,D,E,15,8,J0) L(VG_RMD_F4,E,A,B,C,D,8,11,J0)
+    L(VG_RMD_F4,D,E,A,B,C,1,14,J0) L(VG_RMD_F4,C,D,E,A,B,10,14,J0) L(VG_RMD_F4,B,C,D,E,A,3,12,J0) L(VG_RMD_F4,A,B,C,D,E,12,6,J0)
+#define J1 0x5C4DD124u
+    L(VG_RMD_F3,E,A,B,C,D,6,9,J1) L(VG_RMD_F3,D,E,A,B,C,11,13,J1) L(VG_RMD_F3,C,D,E,A,B,3,15,J1) L(VG_RMD_F3,B,C,D,E,A,7,7,J1)
+    L(VG_RMD_F3,A,B,C,D,E,0,12,J1) L(VG_RMD_F3,E,A,B,C,D,13,8,J1) L(VG_RMD_F3,D,E,A,B,C,5,9,J1) L(VG_RMD_F3,C,D,E,A,B,10,11,J1)
+    L(VG_RMD_F3,B,C,D,E,A,14,7,J1) L(VG_RMD_F3,A,B,C,D,E,15,7,J1) L(VG_RMD_F3,E,A,B,C,D,8,12,J1) L(VG_RMD_F3,D,E,A,B,C,12,7,J1)
+    L(VG_RMD_F3,C,D,E,A,B,4,6,J1) L(VG_RMD_F3,B,C,D,E,A,9,15,J1) L(VG_RMD_F3,A,B,C,D,E,1,13,J1) L(VG_RMD_F3,E,A,B,C,D,2,11,J1)
+#define J2 0x6D703EF3u
+    L(VG_RMD_F2,D,E,A,B,C,15,9,J2) L(VG_RMD_F2,C,D,E,A,B,5,7,J2) L(VG_RMD_F2,B,C,D,E,A,1,15,J2) L(VG_RMD_F2,A,B,C,D,E,3,11,J2)
+    L(VG_RMD_F2,E,A,B,C,D,7,8,J2) L(VG_RMD_F2,D,E,A,B,C,14,6,J2) L(VG_RMD_F2,C,D,E,A,B,6,6,J2) L(VG_RMD_F2,B,C,D,E,A,9,14,J2)
+    L(VG_RMD_F2,A,B,C,D,E,11,12,J2) L(VG_RMD_F2,E,A,B,C,D,8,13,J2) L(VG_RMD_F2,D,E,A,B,C,12,5,J2) L(VG_RMD_F2,C,D,E,A,B,2,14,J2)
+    L(VG_RMD_F2,B,C,D,E,A,10,13,J2) L(VG_RMD_F2,A,B,C,D,E,0,13,J2) L(VG_RMD_F2,E,A,B,C,D,4,7,J2) L(VG_RMD_F2,D,E,A,B,C,13,5,J2)
+#define J3 0x7A6D76E9u
+    L(VG_RMD_F1,C,D,E,A,B,8,15,J3) L(VG_RMD_F1,B,C,D,E,A,6,5,J3) L(VG_RMD_F1,A,B,C,D,E,4,8,J3) L(VG_RMD_F1,E,A,B,C,D,1,11,J3)
+    L(VG_RMD_F1,D,E,A,B,C,3,14,J3) L(VG_RMD_F1,C,D,E,A,B,11,14,J3) L(VG_RMD_F1,B,C,D,E,A,15,6,J3) L(VG_RMD_F1,A,B,C,D,E,0,14,J3)
+    L(VG_RMD_F1,E,A,B,C,D,5,6,J3) L(VG_RMD_F1,D,E,A,B,C,12,9,J3) L(VG_RMD_F1,C,D,E,A,B,2,12,J3) L(VG_RMD_F1,B,C,D,E,A,13,9,J3)
+    L(VG_RMD_F1,A,B,C,D,E,9,12,J3) L(VG_RMD_F1,E,A,B,C,D,7,5,J3) L(VG_RMD_F1,D,E,A,B,C,10,15,J3) L(VG_RMD_F1,C,D,E,A,B,14,8,J3)
+    L(VG_RMD_F0,B,C,D,E,A,12,8,0u) L(VG_RMD_F0,A,B,C,D,E,15,5,0u) L(VG_RMD_F0,E,A,B,C,D,10,12,0u) L(VG_RMD_F0,D,E,A,B,C,4,9,0u)
+    L(VG_RMD_F0,C,D,E,A,B,1,12,0u) L(VG_RMD_F0,B,C,D,E,A,5,5,0u) L(VG_RMD_F0,A,B,C,D,E,8,14,0u) L(VG_RMD_F0,E,A,B,C,D,7,6,0u)
+    L(VG_RMD_F0,D,E,A,B,C,6,8,0u) L(VG_RMD_F0,C,D,E,A,B,2,13,0u) L(VG_RMD_F0,B,C,D,E,A,13,6,0u) L(VG_RMD_F0,A,B,C,D,E,14,5,0u)
+    L(VG_RMD_F0,E,A,B,C,D,0,15,0u) L(VG_RMD_F0,D,E,A,B,C,3,13,0u) L(VG_RMD_F0,C,D,E,A,B,9,11,0u) L(VG_RMD_F0,B,C,D,E,A,11,11,0u)
+#undef L
+    out[0] = h1 + c + D; out[1] = h2 + d + E; out[2] = h3 + e + A; out[3] = h4 + a + B; out[4] = h0 + b + C;
+}
+// hash160 words (little-endian: digest byte 4i+j = byte j of out[i])
+VG_DEV void hash160_pub33(uint32_t out[5], uint32_t prefix, const fe &x) {
+    uint32_t s[8]; sha256_pub33(s, prefix, x); ripemd160_32(out, s);
+}
+VG_DEV void hash160_pub65(uint32_t out[5], const fe &x, const fe &y) {
+    uint32_t s[8]; sha256_pub65(s, x, y); ripemd160_32(out, s);
+}
+// hash160(00 14 || h) : the P2SH-P2WPKH redeem-script hash (src/address.rs:130-135)
+VG_DEV void hash160_p2sh_script(uint32_t out[5], const uint32_t h[5]) {
+    uint32_t B[5], m[6], s[8];
+    VG_UNROLL for (int i = 0; i < 5; i++) B[i] = vg_bswap(h[i]);
+    m[0] = 0x00140000u | (B[0] >> 16);
+    VG_UNROLL for (int i = 1; i < 5; i++) m[i] = (B[i - 1] << 16) | (B[i] >> 16);
+    m[5] = B[4] << 16;
+    uint32_t mm[15];
+    VG_UNROLL for (int i = 0; i < 15; i++) mm[i] = i < 6 ? m[i] : 0u;
+    sha256_short(s, mm, 22);
+    ripemd160_32(out, s);
+}
+
+// ---- Keccak-256 (0x01 padding), state as 25 x 64-bit lanes ----
+VG_CONST uint64_t VG_KECCAK_RC[24] = {
+    0x0000000000000001ULL,0x0000000000008082ULL,0x800000000000808aULL,0x8000000080008000ULL,
+    0x000000000000808bULL,0x0000000080000001ULL,0x8000000080008081ULL,0x8000000000008009ULL,
+    0x000000000000008aULL,0x0000000000000088ULL,0x0000000080008009ULL,0x000000008000000aULL,
+    0x000000008000808bULL,0x800000000000008bULL,0x8000000000008089ULL,0x8000000000008003ULL,
+    0x8000000000008002ULL,0x8000000000000080ULL,0x000000000000800aULL,0x800000008000000aULL,
+    0x8000000080008081ULL,0x8000000000008080ULL,0x0000000080000001ULL,0x8000000080008008ULL};
+
+VG_DEV uint64_t vg_rotl64(uint64_t x, int n) { return (x << n) | (x >> (64 - n)); }
+
+VG_DEV void keccak_f1600(uint64_t s[25]) {
+    for (int r = 0; r < 24; r++) {
+        uint64_t c0 = s[0] ^ s[5] ^ s[10] ^ s[15] ^ s[20], c1 = s[1] ^ s[6] ^ s[11] ^ s[16] ^ s[21];
+        uint64_t c2 = s[2] ^ s[7] ^ s[12] ^ s[17] ^ s[22], c3 = s[3] ^ s[8] ^ s[13] ^ s[18] ^ s[23];
+        uint64_t c4 = s[4] ^ s[9] ^ s[14] ^ s[19] ^ s[24];
+        uint64_t d0 = c4 ^ vg_rotl64(c1, 1), d1 = c0 ^ vg_rotl64(c2, 1), d2 = c1 ^ vg_rotl64(c3, 1);
+        uint64_t d3 = c2 ^ vg_rotl64(c4, 1), d4 = c3 ^ vg_rotl64(c0, 1);
+        uint64_t b[25];
+        b[0] = s[0] ^ d0;
+        b[10] = vg_rotl64(s[1] ^ d1, 1);   b[20] = vg_rotl64(s[2] ^ d2, 62);  b[5] = vg_rotl64(s[3] ^ d3, 28);   b[15] = vg_rotl64(s[4] ^ d4, 27);
+        b[16] = vg_rotl64(s[5] ^ d0, 36);  b[1] = vg_rotl64(s[6] ^ d1, 44);   b[11] = vg_rotl64(s[7] ^ d2, 6);   b[21] = vg_rotl64(s[8] ^ d3, 55);
+        b[6] = vg_rotl64(s[9] ^ d4, 20);   b[7] = vg_rotl64(s[10] ^ d0, 3);   b[17] = vg_rotl64(s[11] ^ d1, 10); b[2] = vg_rotl64(s[12] ^ d2, 43);
+        b[12] = vg_rotl64(s[13] ^ d3, 25); b[22] = vg_rotl64(s[14] ^ d4, 39); b[23] = vg_rotl64(s[15] ^ d0, 41); b[8] = vg_rotl64(s[16] ^ d1, 45);
+        b[18] = vg_rotl64(s[17] ^ d2, 15); b[3] = vg_rotl64(s[18] ^ d3, 21);  b[13] = vg_rotl64(s[19] ^ d4, 8);  b[14] = vg_rotl64(s[20] ^ d0, 18);
+        b[24] = vg_rotl64(s[21] ^ d1, 2);  b[9] = vg_rotl64(s[22] ^ d2, 61);  b[19] = vg_rotl64(s[23] ^ d3, 56); b[4] = vg_rotl64(s[24] ^ d4, 14);
+        VG_UNROLL for (int j = 0; j < 25; j += 5) {
+            s[j + 0] = b[j + 0] ^ (~b[j + 1] & b[j + 2]); s[j + 1] = b[j + 1] ^ (~b[j + 2] & b[j + 3]);
+            s[j + 2] = b[j + 2] ^ (~b[j + 3] & b[j + 4]); s[j + 3] = b[j + 3] ^ (~b[j + 4] & b[j + 0]);
+            s[j + 4] = b[j + 4] ^ (~b[j + 0] & b[j + 1]);
+        }
+        s[0] ^= VG_KECCAK_RC[r];
+    }
+}
+// Ethereum address words: Keccak-256(X || Y)[12..32] as 5 words, digest byte 4i+j = byte j of out[i]
+VG_DEV void keccak_eth_address(uint32_t out[5], const fe &x, const fe &y) {
+    uint64_t s[25];
+    VG_UNROLL for (int i = 0; i < 4; i++) {
+        s[i] = (uint64_t)vg_bswap(x.v[7 - 2 * i]) | ((uint64_t)vg_bswap(x.v[6 - 2 * i]) << 32);
+        s[4 + i] = (uint64_t)vg_bswap(y.v[7 - 2 * i]) | ((uint64_t)vg_bswap(y.v[6 - 2 * i]) << 32);
+    }
+    s[8] = 0x01ULL;
+    VG_UNROLL for (int i = 9; i < 25; i++) s[i] = 0;
+    s[16] = 0x8000000000000000ULL;
+    keccak_f1600(s);
+    out[0] = (uint32_t)(s[1] >> 32); out[1] = (uint32_t)s[2]; out[2] = (uint32_t)(s[2] >> 32);
+    out[3] = (uint32_t)s[3]; out[4] = (uint32_t)(s[3] >> 32);
+}
+// Keccak-256 of 40 ASCII bytes (the lowercase hex of an address) -> first 20 digest bytes as 5 LE words
+VG_DEV void keccak_hex40(uint32_t out[5], const uint32_t m[10]) {   // m: message bytes as little-endian words
+    uint64_t s[25];
+    VG_UNROLL for (int i = 0; i < 5; i++) s[i] = (uint64_t)m[2 * i] | ((uint64_t)m[2 * i + 1] << 32);
+    s[5] = 0x01ULL;
+    VG_UNROLL for (int i = 6; i < 25; i++) s[i] = 0;
+    s[16] = 0x8000000000000000ULL;
+    keccak_f1600(s);
+    out[0] = (uint32_t)s[0]; out[1] = (uint32_t)(s[0] >> 32); out[2] = (uint32_t)s[1]; out[3] = (uint32_t)(s[1] >> 32); out[4] = (uint32_t)s[2];
+}

@@ -1,0 +1,408 @@
+// Host driver of the B200 scan path (see engine.h).
+//
+// Window schedule. With G global lanes (shards x GPUs) the keyspace [start, start+N) is cut into a fixed
+// sequence of windows: one small window per lane at each ramp level (so short ranges and dense patterns
+// finish without computing a full-size window), then full-size windows handed out round-robin: lane g
+// takes windows g, g+G, g+2G, ... Each lane therefore walks with a disjoint start scalar and a common
+// stride of G*W keys (the walk kernel adds the stride point (G*W)*G to every centre), there is no
+// device-to-device traffic, and hits come back in ascending key order.
+#include "engine.h"
+#include <algorithm>
+#include <deque>
+#include <string.h>
+
+namespace vg {
+
+#define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { err = std::string(#call) + ": " + cudaGetErrorString(e_); return false; } } while (0)
+
+static const int kCounterWords = 4;
+
+Engine::~Engine() { destroy(); }
+
+void Engine::destroy() {
+    for (auto &L : lanes_) {
+        cudaSetDevice(L.device);
+        if (L.stream) cudaStreamSynchronize(L.stream);
+        for (auto &S : L.slot) {
+            if (S.d_hits) cudaFree(S.d_hits);
+            if (S.d_counters) cudaFree(S.d_counters);
+            if (S.d_degen) cudaFree(S.d_degen);
+            if (S.h_counters) cudaFreeHost(S.h_counters);
+            if (S.done) cudaEventDestroy(S.done);
+        }
+        for (void *p : {(void *)L.d_pow2, (void *)L.d_gtab, (void *)L.d_centers, (void *)L.d_scratch, (void *)L.d_base8,
+                        (void *)L.d_stride_pts, (void *)L.d_dfa_table, (void *)L.d_dfa_accept})
+            if (p) cudaFree(p);
+        if (L.h_hits) cudaFreeHost(L.h_hits);
+        if (L.own_stream && L.stream) cudaStreamDestroy(L.stream);
+        if (L.copy_stream) cudaStreamDestroy(L.copy_stream);
+    }
+    lanes_.clear();
+}
+
+bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::string &err) {
+    int count = 0;
+    cudaError_t ce = cudaGetDeviceCount(&count);
+    if (ce != cudaSuccess || count == 0) { err = std::string("no CUDA device: ") + cudaGetErrorString(ce); return false; }
+    std::vector<int> devs;
+    if (devices && n_devices > 0) devs.assign(devices, devices + n_devices);
+    else devs.push_back(0);
+    for (int d : devs) if (d < 0 || d >= count) { err = "invalid device index " + std::to_string(d); return false; }
+    half_ = 512;
+    int min_sm = 1 << 30;
+    for (int d : devs) {
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, d));
+        if (prop.major < 10) { err = std::string("device ") + prop.name + " is not sm_100 class; this library is built for B200 (sm_100a) only"; return false; }
+        Lane L; L.device = d; L.sm_count = prop.multiProcessorCount; L.name = prop.name;
+        min_sm = std::min(min_sm, L.sm_count);
+        lanes_.push_back(L);
+    }
+    uint32_t full_blocks = (uint32_t)min_sm * 2;       // __launch_bounds__(256, 2): two resident CTAs per SM
+    if (hint) full_blocks = std::max<uint32_t>(1, std::min<uint32_t>(hint / (VG_BLOCK * 2 * half_), 8u * min_sm));
+    levels_.clear();
+    for (uint32_t b : {1u, 8u, 64u}) if (b * 4 <= full_blocks) levels_.push_back({b, b * VG_BLOCK, (uint64_t)b * VG_BLOCK * 2 * half_});
+    levels_.push_back({full_blocks, full_blocks * VG_BLOCK, (uint64_t)full_blocks * VG_BLOCK * 2 * half_});
+    const Level &F = levels_.back();
+    for (auto &L : lanes_) {
+        CK(cudaSetDevice(L.device));
+        CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&L.copy_stream, cudaStreamNonBlocking));
+        CK(cudaMalloc(&L.d_pow2, 256 * 16 * 4));
+        CK(cudaMalloc(&L.d_gtab, (size_t)half_ * 16 * 4));
+        CK(cudaMalloc(&L.d_centers, (size_t)16 * F.threads * 4));
+        CK(cudaMalloc(&L.d_scratch, (size_t)(half_ + 1) * 8 * F.threads * 4));
+        CK(cudaMalloc(&L.d_base8, 64));
+        CK(cudaMalloc(&L.d_stride_pts, 16 * 4 * 8));
+        for (auto &S : L.slot) {
+            CK(cudaMalloc(&S.d_hits, (size_t)F.window * sizeof(vg_hit_rec)));
+            CK(cudaMalloc(&S.d_counters, kCounterWords * 4));
+            CK(cudaMalloc(&S.d_degen, (size_t)F.threads * 4));
+            CK(cudaHostAlloc(&S.h_counters, kCounterWords * 4, cudaHostAllocDefault));
+            CK(cudaEventCreateWithFlags(&S.done, cudaEventDisableTiming));
+        }
+        L.h_hits_cap = 1u << 20;
+        CK(cudaHostAlloc(&L.h_hits, L.h_hits_cap * sizeof(vg_hit_rec), cudaHostAllocDefault));
+        CK(launch_build_tables(L.d_pow2, L.d_gtab, half_, L.stream));
+        launches += 2;
+        CK(cudaStreamSynchronize(L.stream));
+    }
+    return true;
+}
+
+bool Engine::set_stream(int lane, cudaStream_t s, std::string &err) {
+    if (lane < 0 || lane >= (int)lanes_.size()) { err = "invalid lane"; return false; }
+    Lane &L = lanes_[lane];
+    CK(cudaSetDevice(L.device));
+    CK(cudaStreamSynchronize(L.stream));
+    if (L.own_stream) cudaStreamDestroy(L.stream);
+    L.stream = s; L.own_stream = false;
+    return true;
+}
+
+bool Engine::set_shard(uint32_t index, uint32_t count, std::string &err) {
+    if (count == 0 || index >= count) { err = "invalid shard index/count"; return false; }
+    shard_index_ = index; shard_count_ = count; stride_lanes_ = 0;
+    return true;
+}
+
+bool Engine::upload_dfa(std::string &err) {
+    const Dfa &d = lp_.dfa;
+    for (auto &L : lanes_) {
+        CK(cudaSetDevice(L.device));
+        if (L.d_dfa_table) { cudaFree(L.d_dfa_table); L.d_dfa_table = nullptr; }
+        if (L.d_dfa_accept) { cudaFree(L.d_dfa_accept); L.d_dfa_accept = nullptr; }
+        CK(cudaMalloc(&L.d_dfa_table, d.table.size() * 2));
+        CK(cudaMalloc(&L.d_dfa_accept, d.accept_end.size()));
+        CK(cudaMemcpy(L.d_dfa_table, d.table.data(), d.table.size() * 2, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(L.d_dfa_accept, d.accept_end.data(), d.accept_end.size(), cudaMemcpyHostToDevice));
+    }
+    return true;
+}
+
+bool Engine::set_pattern(int format, const std::string &pattern, bool ci, std::string &err) {
+    LoweredPattern lp;
+    if (!lower_pattern(format, pattern, ci, lp, err)) return false;
+    lp_ = lp;
+    lp_.dev.dfa.n_states = lp_.dfa.n_states; lp_.dev.dfa.n_classes = lp_.dfa.n_classes; lp_.dev.dfa.start = lp_.dfa.start;
+    for (int c = 0; c < 128; c++) lp_.dev.dfa.class_of[c] = lp_.dfa.class_of[c];
+    has_pattern_ = true;
+    return upload_dfa(err);
+}
+
+// stride point of the final level for the current global lane count: (G * W_final) * G
+bool Engine::compute_stride_points(std::string &err) {
+    uint32_t G = shard_count_ * (uint32_t)lanes_.size();
+    if (stride_lanes_ == G) return true;
+    for (auto &L : lanes_) {
+        CK(cudaSetDevice(L.device));
+        L.stride_pt.assign(levels_.size(), {});
+        for (size_t lv = 0; lv < levels_.size(); lv++) {
+            // every level uses its own G*W stride; only the final level's next centre is ever consumed
+            U256 k = U256(levels_[lv].window).mul64(G);
+            uint32_t k8[8]; k.to_limbs32(k8);
+            CK(cudaMemcpyAsync(L.d_base8, k8, 32, cudaMemcpyHostToDevice, L.stream));
+            CK(launch_points_of_scalars(L.d_stride_pts, 1, L.d_base8, 0, L.d_pow2, L.stream));
+            launches++;
+            CK(cudaMemcpyAsync(L.stride_pt[lv].data(), L.d_stride_pts, 64, cudaMemcpyDeviceToHost, L.stream));
+            CK(cudaStreamSynchronize(L.stream));
+        }
+        L.centers_level = -1;
+    }
+    stride_lanes_ = G;
+    return true;
+}
+
+bool Engine::setup_centers(Lane &L, int level, const U256 &window_base, std::string &err) {
+    const Level &V = levels_[level];
+    U256 first = window_base.add64(half_);
+    uint32_t k8[8]; first.to_limbs32(k8);
+    CK(cudaMemcpyAsync(L.d_base8, k8, 32, cudaMemcpyHostToDevice, L.stream));
+    CK(launch_points_of_scalars(L.d_centers, V.threads, L.d_base8, 2ull * half_, L.d_pow2, L.stream));
+    launches++;
+    L.centers_level = level;
+    return true;
+}
+
+void Engine::fill_params(Lane &L, Slot &S, vg_scan_params &P) {
+    const Level &V = levels_[S.level];
+    memset(&P, 0, sizeof P);
+    P.n_threads = V.threads; P.half = half_;
+    P.centers = L.d_centers; P.scratch = L.d_scratch; P.gtab = L.d_gtab;
+    memcpy(P.stride_pt, L.stride_pt[S.level].data(), 64);
+    P.limit = S.limit;
+    P.hits = S.d_hits; P.hit_count = S.d_counters; P.hit_cap = (uint32_t)std::min<uint64_t>(V.window, 0xffffffffu);
+    P.degen_list = S.d_degen; P.degen_count = S.d_counters + 1; P.degen_cap = V.threads;
+    P.m = lp_.dev;
+    P.m.dfa.table = L.d_dfa_table; P.m.dfa.accept = L.d_dfa_accept;
+}
+
+bool Engine::launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uint32_t dump_stride, std::string &err) {
+    Slot &S = L.slot[s];
+    vg_scan_params P; fill_params(L, S, P);
+    P.dump = dump; P.dump_stride = dump_stride;
+    CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
+    CK(launch_walk(fmt, mode, P, levels_[S.level].blocks, L.stream));
+    launches++;
+    CK(cudaMemcpyAsync(S.h_counters, S.d_counters, kCounterWords * 4, cudaMemcpyDeviceToHost, L.stream));
+    CK(cudaEventRecord(S.done, L.stream));
+    S.busy = true;
+    return true;
+}
+
+namespace {
+struct LaneRun { int level = 0; uint64_t k = 0; bool done = false; U256 expect_base; bool have_expect = false; };
+}
+
+bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, const volatile int32_t *stop, const Progress &progress,
+                  std::vector<Hit> &hits, uint64_t &keys_scanned, std::string &err) {
+    hits.clear(); keys_scanned = 0;
+    if (!has_pattern_) { err = "no pattern set"; return false; }
+    if (lp_.format == VG_FMT_P2TR) { err = "P2TR is not supported by the CUDA scan path yet"; return false; }
+    // valid scalars are 1..n-1 (src/address.rs:93); scalars outside are skipped, not counted (src/scanner.rs:294-295)
+    U256 start = start_in, end = end_in ? *end_in : secp_order_minus1();
+    if (end_in && end < start) { err = "range end is below range start"; return false; }
+    if (start.is_zero()) start = U256(1);
+    if (secp_order_minus1() < end) end = secp_order_minus1();
+    if (end < start) return true;                      // nothing valid in range
+    if (lp_.dev.kind == VG_MATCH_INTERVALS && lp_.dev.n_intervals == 0) {
+        // the pattern can never match an address of this format: the reference would scan to the end of the range
+        // and find nothing; report the range as scanned without launching
+        U256 n = end.sub(start).add64(1);
+        keys_scanned = n.fits64() ? n.w[0] : ~0ULL;
+        return true;
+    }
+    const U256 N = end.sub(start).add64(1);            // >= 1; cannot wrap because end <= n-1 < 2^256-1
+    if (!compute_stride_points(err)) return false;
+    const uint32_t nl = (uint32_t)lanes_.size(), G = shard_count_ * nl;
+    const int fl = (int)levels_.size() - 1;
+    std::vector<U256> level_base(levels_.size());
+    for (int lv = 1; lv <= fl; lv++) level_base[lv] = level_base[lv - 1].add(U256(levels_[lv - 1].window).mul64(G));
+    std::vector<LaneRun> runs(nl);
+    uint64_t seq = 0;
+    const int fmt = lp_.format;
+
+    auto next_offset = [&](uint32_t li) -> U256 {
+        const LaneRun &r = runs[li];
+        uint64_t gl = (uint64_t)shard_index_ * nl + li;
+        U256 idx = r.level < fl ? U256(gl) : U256(r.k).mul64(G).add64(gl);
+        // idx * window (idx < 2^64 * 2^32 safely inside 256 bits)
+        U256 off = idx.mul64(levels_[r.level].window);
+        return level_base[r.level].add(off);
+    };
+    std::deque<std::pair<uint32_t, int>> inflight;
+    auto issue = [&](uint32_t li) -> bool {
+        Lane &L = lanes_[li]; LaneRun &r = runs[li];
+        if (r.done) return true;
+        int s = !L.slot[0].busy ? 0 : (!L.slot[1].busy ? 1 : -1);
+        if (s < 0) return true;
+        U256 off = next_offset(li);
+        if (!(off < N)) { r.done = true; return true; }
+        if (cudaSetDevice(L.device) != cudaSuccess) { err = "cudaSetDevice failed"; return false; }
+        Slot &S = L.slot[s];
+        S.base = start.add(off); S.level = r.level; S.seq = seq++;
+        U256 remain = N.sub(off);
+        S.limit = (remain.fits64() && remain.w[0] < levels_[r.level].window) ? remain.w[0] : levels_[r.level].window;
+        if (L.centers_level != r.level || !r.have_expect || !(r.expect_base == S.base)) {
+            if (!setup_centers(L, r.level, S.base, err)) return false;
+        }
+        if (!launch_window(L, s, fmt, VG_MODE_MATCH, nullptr, 0, err)) return false;
+        // after this launch the centres stand at base + G*W of the same level
+        r.expect_base = S.base.add(U256(levels_[r.level].window).mul64(G)); r.have_expect = true;
+        if (r.level < fl) { r.level++; r.have_expect = false; } else r.k++;
+        inflight.push_back({li, s});
+        return true;
+    };
+    auto collect = [&](uint32_t li, int s, bool keep) -> bool {
+        Lane &L = lanes_[li]; Slot &S = L.slot[s];
+        CK(cudaSetDevice(L.device));
+        CK(cudaEventSynchronize(S.done));
+        S.busy = false;
+        if (!keep) return true;
+        uint32_t n_hits = S.h_counters[0], n_degen = S.h_counters[1];
+        if (n_degen) {
+            // batches that touched the point at infinity or collided with a table point: redo them key by key
+            vg_scan_params P; fill_params(L, S, P);
+            uint32_t k8[8]; S.base.to_limbs32(k8);
+            CK(cudaStreamSynchronize(L.stream));          // the other slot's window may still be running; d_base8 is shared
+            bool other_busy = L.slot[1 - s].busy;
+            CK(cudaMemcpyAsync(L.d_base8, k8, 32, cudaMemcpyHostToDevice, L.stream));
+            CK(launch_slow(fmt, VG_MODE_MATCH, P, L.d_base8, L.d_pow2, std::min(n_degen, levels_[S.level].threads), L.stream));
+            launches++;
+            CK(cudaMemcpyAsync(S.h_counters, S.d_counters, kCounterWords * 4, cudaMemcpyDeviceToHost, L.stream));
+            CK(cudaStreamSynchronize(L.stream));
+            n_hits = S.h_counters[0];
+            L.centers_level = -1;                         // centres of the flagged threads are void: set up again
+            runs[li].have_expect = false;
+            (void)other_busy;
+        }
+        uint64_t cap = levels_[S.level].window;
+        if (n_hits > cap) n_hits = (uint32_t)cap;         // cannot happen: at most one hit per key
+        size_t before = hits.size();
+        for (uint32_t done = 0; done < n_hits;) {
+            uint32_t chunk = (uint32_t)std::min<size_t>(n_hits - done, L.h_hits_cap);
+            CK(cudaMemcpyAsync(L.h_hits, S.d_hits + done, (size_t)chunk * sizeof(vg_hit_rec), cudaMemcpyDeviceToHost, L.copy_stream));
+            CK(cudaStreamSynchronize(L.copy_stream));
+            for (uint32_t i = 0; i < chunk; i++) {
+                const vg_hit_rec &R = L.h_hits[i];
+                Hit h; memset(h.digest, 0, 32);
+                h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = li;
+                for (int w = 0; w < 8; w++) for (int b = 0; b < 4; b++) h.digest[4 * w + b] = (uint8_t)(R.digest[w] >> (8 * b));
+                // exact confirmation on the host: re-encode the address from the digest and run the full DFA
+                std::string addr = format_address(fmt, h.digest);
+                if (!lp_.dfa.match(addr.data(), addr.size())) continue;
+                h.key = S.base.add64(((uint64_t)R.idx_hi << 32) | R.idx_lo);
+                hits.push_back(h);
+            }
+            done += chunk;
+        }
+        std::sort(hits.begin() + before, hits.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
+        keys_scanned += S.limit;
+        return true;
+    };
+
+    bool stopping = false;
+    for (int round = 0; round < 2; round++) for (uint32_t li = 0; li < nl; li++) if (!issue(li)) return false;
+    while (!inflight.empty()) {
+        auto [li, s] = inflight.front(); inflight.pop_front();
+        if (!collect(li, s, !stopping)) return false;
+        if (!stopping) {
+            if (progress) progress(keys_scanned);
+            if (stop && *stop) stopping = true;
+            if (max_hits && hits.size() >= max_hits) stopping = true;
+        }
+        if (!stopping && !issue(li)) return false;
+    }
+    for (auto &L : lanes_) { CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); L.centers_level = -1; }
+    std::sort(hits.begin(), hits.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
+    if (max_hits && hits.size() > max_hits) hits.resize(max_hits);
+    return true;
+}
+
+bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *out, uint32_t stride, std::string &err) {
+    if (format < 0 || format > 5 || stride == 0 || stride > 32) { err = "invalid format or stride"; return false; }
+    if (n == 0) return true;
+    if (n > (1ull << 28)) { err = "digest_batch is limited to 2^28 keys per call"; return false; }
+    Lane &L = lanes_[0];
+    CK(cudaSetDevice(L.device));
+    uint32_t saved_idx = shard_index_, saved_cnt = shard_count_;
+    shard_index_ = 0; shard_count_ = 1; stride_lanes_ = 0;
+    // single lane, stride = one window: emulate G = 1 by computing stride points for one lane only
+    std::vector<Lane> others;
+    if (lanes_.size() > 1) { others.assign(lanes_.begin() + 1, lanes_.end()); lanes_.resize(1); }
+    bool ok = compute_stride_points(err);
+    uint8_t *d_out = nullptr;
+    auto restore = [&]() {
+        if (d_out) cudaFree(d_out);
+        for (auto &o : others) lanes_.push_back(o);
+        shard_index_ = saved_idx; shard_count_ = saved_cnt; stride_lanes_ = 0;
+    };
+    if (!ok) { restore(); return false; }
+    Lane &L0 = lanes_[0];
+    if (cudaMalloc(&d_out, (size_t)n * stride) != cudaSuccess) { err = "cudaMalloc failed for the digest buffer"; restore(); return false; }
+    cudaMemsetAsync(d_out, 0, (size_t)n * stride, L0.stream);
+    // pick the smallest level whose window covers n, else the full level
+    int level = (int)levels_.size() - 1;
+    for (int lv = 0; lv < (int)levels_.size(); lv++) if (levels_[lv].window >= n) { level = lv; break; }
+    const uint64_t W = levels_[level].window;
+    LoweredPattern saved = lp_;
+    memset(&lp_.dev, 0, sizeof lp_.dev);
+    bool good = true;
+    U256 base = start;
+    for (uint64_t off = 0; off < n && good; off += W) {
+        Slot &S = L0.slot[0];
+        S.base = base; S.level = level; S.limit = std::min<uint64_t>(W, n - off);
+        if (off == 0) good = setup_centers(L0, level, base, err);
+        if (good) good = launch_window(L0, 0, format, VG_MODE_DUMP, d_out + off * stride, stride, err);
+        if (good && cudaStreamSynchronize(L0.stream) != cudaSuccess) { err = "walk kernel failed"; good = false; }
+        S.busy = false;
+        if (good && S.h_counters[1]) {
+            vg_scan_params P; fill_params(L0, S, P);
+            P.dump = d_out + off * stride; P.dump_stride = stride;
+            uint32_t k8[8]; base.to_limbs32(k8);
+            cudaMemcpyAsync(L0.d_base8, k8, 32, cudaMemcpyHostToDevice, L0.stream);
+            cudaError_t e = launch_slow(format, VG_MODE_DUMP, P, L0.d_base8, L0.d_pow2, std::min(S.h_counters[1], levels_[level].threads), L0.stream);
+            launches++;
+            if (e != cudaSuccess || cudaStreamSynchronize(L0.stream) != cudaSuccess) { err = "slow kernel failed"; good = false; }
+            if (good && off + W < n) good = setup_centers(L0, level, base.add64(W), err);
+        }
+        base = base.add64(W);
+    }
+    if (good && cudaMemcpy(out, d_out, (size_t)n * stride, cudaMemcpyDeviceToHost) != cudaSuccess) { err = "copy of digests failed"; good = false; }
+    L0.centers_level = -1;
+    lp_ = saved;
+    restore();
+    return good;
+}
+
+bool Engine::bench_resident(const U256 &start, uint32_t n_windows, float &ms, uint64_t &keys, uint64_t &nlaunch, std::string &err) {
+    if (!has_pattern_) { err = "no pattern set"; return false; }
+    if (!compute_stride_points(err)) return false;
+    Lane &L = lanes_[0];
+    CK(cudaSetDevice(L.device));
+    const int fl = (int)levels_.size() - 1;
+    uint64_t gl = (uint64_t)shard_index_ * lanes_.size();
+    U256 base = start.add(U256(gl).mul64(levels_[fl].window));
+    if (!setup_centers(L, fl, base, err)) return false;
+    Slot &S = L.slot[0];
+    S.base = base; S.level = fl; S.limit = levels_[fl].window;
+    vg_scan_params P; fill_params(L, S, P);
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    CK(cudaStreamSynchronize(L.stream));
+    CK(cudaEventRecord(e0, L.stream));
+    for (uint32_t w = 0; w < n_windows; w++) {
+        CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
+        CK(launch_walk(lp_.format, VG_MODE_MATCH, P, levels_[fl].blocks, L.stream));
+    }
+    CK(cudaEventRecord(e1, L.stream));
+    CK(cudaEventSynchronize(e1));
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    launches += n_windows; nlaunch = n_windows;
+    keys = (uint64_t)n_windows * levels_[fl].window;
+    L.centers_level = -1;
+    return true;
+}
+
+}  // namespace vg

@@ -1,0 +1,215 @@
+// Pattern lowering: (format, regex) -> device matcher.
+//   ^literal...   -> inclusive intervals over the leading 64 digest bits (no per-key Base58/Bech32 encode)
+//   ^address$     -> exact digest compare (the address is decoded once on the host)
+//   anything else -> dense DFA over the on-GPU address encode
+// Every device hit is re-checked on the host with the full DFA over the re-encoded address string, so
+// interval bounds only need to be supersets (they are exact up to the 4 Base58Check checksum bytes).
+// Reference semantics: src/pattern.rs:21-45 (match = regex search on the address string),
+// src/provider.rs:55-63 (prefix / exact pattern shapes), src/address.rs:92-151 (formats).
+#include "lowering.h"
+#include <algorithm>
+#include <string.h>
+
+namespace vg {
+namespace {
+
+const char *alphabet_for(int format) {
+    switch (format) {
+        case VG_FMT_P2PKH: case VG_FMT_P2PKH_UNCOMPRESSED: case VG_FMT_P2SH_P2WPKH: return B58_ALPHABET;
+        case VG_FMT_P2WPKH: case VG_FMT_P2TR: return "qpzry9x8gf2tvdw0s3jn54khce6mua7lb1";   // data charset + hrp/separator chars
+        default: return "0123456789abcdefABCDEFx";
+    }
+}
+typedef std::pair<U256, U256> Range;   // inclusive range over the digest read as a big-endian integer of `bits` bits
+
+U256 pow58(unsigned e) { U256 r(1); for (unsigned i = 0; i < e; i++) r = r.mul64(58); return r; }
+U256 umax(const U256 &a, const U256 &b) { return a < b ? b : a; }
+U256 umin(const U256 &a, const U256 &b) { return a < b ? a : b; }
+
+// Base58Check payload = version || h160 || checksum4 (25 bytes)
+void base58_ranges(int version, const std::string &p, std::vector<Range> &out) {
+    size_t a = 0;
+    while (a < p.size() && p[a] == '1') a++;
+    std::string rest = p.substr(a);
+    const U256 max160 = U256::pow2(160).sub(U256(1));
+    if (rest.empty()) {
+        if (a == 0) { out.push_back({U256(0), max160}); return; }
+        if (version != 0) return;
+        // at least a leading zero bytes in the 25-byte payload: h160||ck < 2^(8*(25-a))
+        if (a > 25) return;
+        unsigned bits = 8 * (25 - (unsigned)a);
+        U256 hi = bits >= 32 ? U256::pow2(bits).sub(U256(1)).shr(32) : U256(0);
+        out.push_back({U256(0), umin(hi, max160)});
+        return;
+    }
+    U256 zlo, zhi, verbase;
+    if (version == 0) {
+        if (a < 1 || a > 24) return;
+        zlo = U256::pow2(8 * (24 - (unsigned)a)); zhi = U256::pow2(8 * (25 - (unsigned)a)).sub(U256(1));
+    } else {
+        if (a != 0) return;
+        verbase = U256((uint64_t)version).shl(192);
+        zlo = verbase; zhi = U256((uint64_t)version + 1).shl(192).sub(U256(1));
+    }
+    U256 val; size_t r = rest.size();
+    for (char c : rest) {
+        const char *q = strchr(B58_ALPHABET, c);
+        if (!q || !c) return;
+        val = val.mul64(58).add64((uint64_t)(q - B58_ALPHABET));
+    }
+    for (unsigned D = (unsigned)r; D <= 35; D++) {
+        U256 dlo = pow58(D - 1), dhi = pow58(D).sub(U256(1));
+        U256 scale = pow58(D - (unsigned)r);
+        uint64_t ov1 = 0;
+        U256 plo = val;
+        // val * 58^(D-r): multiply stepwise to detect overflow
+        bool overflow = false;
+        for (unsigned i = 0; i < D - r; i++) { plo = plo.mul64(58, &ov1); if (ov1) { overflow = true; break; } }
+        if (overflow) break;
+        bool carry = false;
+        U256 phi = plo.add(scale.sub(U256(1)), &carry);
+        if (carry) phi = U256(0).sub(U256(1));   // saturate at 2^256 - 1
+        U256 lo = umax(umax(dlo, zlo), plo), hi = umin(umin(dhi, zhi), phi);
+        if (hi < lo) continue;
+        out.push_back({lo.sub(verbase).shr(32), hi.sub(verbase).shr(32)});
+    }
+}
+// bech32 data characters after "bc1<q|p>" map 5 bits each onto the top of the witness program
+void bech32_ranges(char verchar, unsigned prog_bits, const std::string &p, std::vector<Range> &out) {
+    const std::string head = std::string("bc1") + verchar;
+    const U256 maxv = U256::pow2(prog_bits).sub(U256(1));
+    size_t n = std::min(p.size(), head.size());
+    if (p.compare(0, n, head, 0, n) != 0) return;
+    if (p.size() <= head.size()) { out.push_back({U256(0), maxv}); return; }
+    unsigned max_chars = prog_bits / 5;   // whole characters that lie inside the program
+    U256 bits; unsigned r = 0;
+    for (size_t i = head.size(); i < p.size() && r < max_chars; i++, r++) {
+        const char *q = strchr(BECH32_ALPHABET, p[i]);
+        if (!q || !p[i]) return;
+        bits = bits.shl(5).add64((uint64_t)(q - BECH32_ALPHABET));
+    }
+    unsigned sh = prog_bits - 5 * r;
+    out.push_back({bits.shl(sh), bits.add64(1).shl(sh).sub(U256(1))});
+}
+void hex_ranges(const std::string &p, std::vector<Range> &out) {
+    const std::string head = "0x";
+    const U256 maxv = U256::pow2(160).sub(U256(1));
+    size_t n = std::min(p.size(), head.size());
+    if (p.compare(0, n, head, 0, n) != 0) return;
+    if (p.size() <= 2) { out.push_back({U256(0), maxv}); return; }
+    U256 bits; unsigned r = 0;
+    for (size_t i = 2; i < p.size() && r < 40; i++, r++) {
+        int c = p[i], v;
+        if (c >= '0' && c <= '9') v = c - '0';
+        else if (c >= 'a' && c <= 'f') v = c - 'a' + 10;
+        else if (c >= 'A' && c <= 'F') v = c - 'A' + 10;
+        else return;
+        bits = bits.shl(4).add64((uint64_t)v);
+    }
+    unsigned sh = 160 - 4 * r;
+    out.push_back({bits.shl(sh), bits.add64(1).shl(sh).sub(U256(1))});
+}
+void ranges_for(int format, const std::string &p, std::vector<Range> &out) {
+    switch (format) {
+        case VG_FMT_P2PKH: case VG_FMT_P2PKH_UNCOMPRESSED: base58_ranges(0, p, out); break;
+        case VG_FMT_P2SH_P2WPKH: base58_ranges(5, p, out); break;
+        case VG_FMT_P2WPKH: bech32_ranges('q', 160, p, out); break;
+        case VG_FMT_P2TR: bech32_ranges('p', 256, p, out); break;
+        default: hex_ranges(p, out); break;
+    }
+}
+// exact address -> digest; false if the string is not a valid address of this format
+bool decode_exact(int format, const std::string &addr, uint8_t digest[32]) {
+    std::vector<uint8_t> payload; int witver;
+    memset(digest, 0, 32);
+    switch (format) {
+        case VG_FMT_P2PKH: case VG_FMT_P2PKH_UNCOMPRESSED: case VG_FMT_P2SH_P2WPKH:
+            if (!h_base58check_decode(addr, payload) || payload.size() != 21) return false;
+            if (payload[0] != (format == VG_FMT_P2SH_P2WPKH ? 5 : 0)) return false;
+            if (h_base58check(payload.data(), 21) != addr) return false;   // canonical form only
+            memcpy(digest, payload.data() + 1, 20); return true;
+        case VG_FMT_P2WPKH:
+            if (!h_segwit_decode(addr, witver, payload) || witver != 0 || payload.size() != 20) return false;
+            memcpy(digest, payload.data(), 20); return true;
+        case VG_FMT_P2TR:
+            if (!h_segwit_decode(addr, witver, payload) || witver != 1 || payload.size() != 32) return false;
+            memcpy(digest, payload.data(), 32); return true;
+        default: {
+            if (addr.size() != 42 || addr[0] != '0' || addr[1] != 'x') return false;
+            for (int i = 0; i < 20; i++) {
+                int v = 0;
+                for (int j = 0; j < 2; j++) {
+                    int c = addr[2 + 2 * i + j], d;
+                    if (c >= '0' && c <= '9') d = c - '0'; else if (c >= 'a' && c <= 'f') d = c - 'a' + 10; else if (c >= 'A' && c <= 'F') d = c - 'A' + 10; else return false;
+                    v = v * 16 + d;
+                }
+                digest[i] = (uint8_t)v;
+            }
+            return h_eip55(digest) == addr;   // the reference matches the EIP-55 form, case-sensitively
+        }
+    }
+}
+}  // namespace
+
+bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPattern &out, std::string &err) {
+    out = LoweredPattern();
+    out.format = format; out.pattern = pattern; out.case_insensitive = ci;
+    if (format < 0 || format > 5) { err = "invalid address format"; return false; }
+    if (!compile_pattern(pattern, ci, out.dfa, out.info, err)) { err = "Invalid regex pattern: " + pattern + ": " + err; return false; }   // src/pattern.rs:32-33
+    memset(&out.dev, 0, sizeof out.dev);
+    out.dev.kind = VG_MATCH_DFA;
+    out.kind_name = "dfa";
+    const PatternInfo &info = out.info;
+    if (!info.anchored_start || info.prefix_sets.empty()) return true;
+
+    // expand the leading sets into literal prefixes (restricted to characters this format can produce)
+    const char *alpha = alphabet_for(format);
+    std::vector<std::string> prefixes{""};
+    bool truncated = false;
+    for (const auto &set : info.prefix_sets) {
+        std::string chars;
+        for (const char *a = alpha; *a; a++) if (set[(unsigned char)*a] && chars.find(*a) == std::string::npos) chars.push_back(*a);
+        if (chars.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; return true; }   // can never match
+        if (prefixes.size() * chars.size() > 64) { truncated = true; break; }
+        std::vector<std::string> nx;
+        for (const auto &p : prefixes) for (char c : chars) nx.push_back(p + c);
+        prefixes.swap(nx);
+    }
+    if (prefixes.size() == 1 && prefixes[0].empty()) return true;
+
+    if (!truncated && info.rest_is_end && prefixes.size() == 1) {
+        uint8_t dg[32];
+        if (!decode_exact(format, prefixes[0], dg)) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; return true; }
+        out.dev.kind = VG_MATCH_EXACT; out.kind_name = "exact";
+        out.dev.exact_words = digest_len_of_format(format) / 4;
+        for (int i = 0; i < 8; i++) out.dev.exact[i] = (uint32_t)dg[4 * i] | (uint32_t)dg[4 * i + 1] << 8 | (uint32_t)dg[4 * i + 2] << 16 | (uint32_t)dg[4 * i + 3] << 24;
+        return true;
+    }
+    std::vector<Range> ranges;
+    for (const auto &p : prefixes) ranges_for(format, p, ranges);
+    // reduce to the leading 64 digest bits, merge
+    unsigned bits = format == VG_FMT_P2TR ? 256 : 160;
+    std::vector<std::pair<uint64_t, uint64_t>> r64;
+    for (auto &r : ranges) r64.push_back({r.first.shr(bits - 64).w[0], r.second.shr(bits - 64).w[0]});
+    std::sort(r64.begin(), r64.end());
+    std::vector<std::pair<uint64_t, uint64_t>> merged;
+    for (auto &r : r64) {
+        if (!merged.empty() && (r.first <= merged.back().second || r.first == merged.back().second + 1)) merged.back().second = std::max(merged.back().second, r.second);
+        else merged.push_back(r);
+    }
+    if (merged.size() > VG_MAX_INTERVALS) return true;   // too fragmented: keep the DFA path
+    if (merged.size() == 1 && merged[0].first == 0 && merged[0].second == ~0ULL) {
+        // the prefix constrains nothing (e.g. ^1 on P2PKH, ^bc1q on P2WPKH): only worth a prefilter if the rest does
+        if (info.rest_empty && !truncated) { out.dev.kind = VG_MATCH_ALL; out.kind_name = "all"; }
+        return true;
+    }
+    out.dev.kind = VG_MATCH_INTERVALS; out.kind_name = "intervals";
+    out.dev.n_intervals = (int)merged.size();
+    for (size_t i = 0; i < merged.size(); i++) {
+        out.dev.lo_hi[i][0] = (uint32_t)(merged[i].first >> 32); out.dev.lo_hi[i][1] = (uint32_t)merged[i].first;
+        out.dev.lo_hi[i][2] = (uint32_t)(merged[i].second >> 32); out.dev.lo_hi[i][3] = (uint32_t)merged[i].second;
+    }
+    return true;
+}
+
+}  // namespace vg

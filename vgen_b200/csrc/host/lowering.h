@@ -1,0 +1,19 @@
+// Result of lowering a (format, pattern) pair; see lowering.cpp.
+#pragma once
+#include <string>
+#include "host_util.h"
+#include "regex_dfa.h"
+#include "../scan_types.h"
+
+namespace vg {
+struct LoweredPattern {
+    int format = 0;
+    std::string pattern;
+    bool case_insensitive = false;
+    Dfa dfa;                 // exact matcher on the address string (host confirm + device DFA path)
+    PatternInfo info;
+    vg_matcher_dev dev;      // device matcher (DFA table pointers are filled by the engine per device)
+    std::string kind_name;   // "intervals" | "exact" | "dfa" | "all" | "none"
+};
+bool lower_pattern(int format, const std::string &pattern, bool case_insensitive, LoweredPattern &out, std::string &err);
+}

@@ -1,0 +1,37 @@
+// Pattern front end of the product: Rust-`regex` syntax subset -> dense DFA with `is_match`
+// semantics (unanchored search unless ^/$ are written), mirroring Pattern::new / Pattern::matches
+// (src/pattern.rs:21-45). The DFA runs on the host (confirmation, vgen_pattern_is_match) and on the
+// device (match.cuh) over address strings. Also extracts the literal-prefix structure that
+// lowering.cpp turns into digest interval compares.
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <bitset>
+
+namespace vg {
+
+struct Dfa {
+    uint32_t n_states = 0, n_classes = 0, start = 0;
+    std::vector<uint16_t> table;        // [n_states][n_classes]
+    std::vector<uint8_t> accept_end;    // [n_states]: 1 if the input may end here with a match
+    uint8_t class_of[256];
+    bool match(const char *s, size_t n) const {
+        uint32_t st = start;
+        for (size_t i = 0; i < n; i++) st = table[(size_t)st * n_classes + class_of[(uint8_t)s[i]]];
+        return accept_end[st] != 0;
+    }
+};
+
+struct PatternInfo {
+    bool anchored_start = false;                 // pattern is  ^ <sets...> <rest>
+    std::vector<std::bitset<128>> prefix_sets;   // the leading single-character sets after ^
+    bool rest_empty = false;                     // nothing after the sets  (=> prefix match)
+    bool rest_is_end = false;                    // exactly `$` after the sets (=> exact match)
+};
+
+// Returns false and fills err on a syntax error / unsupported construct (same cases as Rust would
+// reject, plus: \b \B, \p{..}, class set operations, flag x, non-ASCII inside classes).
+bool compile_pattern(const std::string &pattern, bool case_insensitive, Dfa &dfa, PatternInfo &info, std::string &err);
+
+}  // namespace vg

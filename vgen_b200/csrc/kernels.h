@@ -1,0 +1,27 @@
+// Launchers implemented in scan_kernels.cu, called by the host engine.
+#pragma once
+#include <cuda_runtime.h>
+#include "scan_types.h"
+
+#define VG_BLOCK 256
+
+namespace vg {
+cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, cudaStream_t s);
+cudaError_t launch_points_of_scalars(uint32_t *out, uint32_t n, const uint32_t *base8_dev, unsigned long long step,
+                                     const uint32_t *pow2, cudaStream_t s);
+cudaError_t launch_walk(int fmt, int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow(int fmt, int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2,
+                        uint32_t n_batches, cudaStream_t s);
+cudaError_t launch_walk_fmt0(int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow_fmt0(int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2, uint32_t n_batches, cudaStream_t s);
+cudaError_t launch_walk_fmt1(int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow_fmt1(int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2, uint32_t n_batches, cudaStream_t s);
+cudaError_t launch_walk_fmt2(int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow_fmt2(int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2, uint32_t n_batches, cudaStream_t s);
+cudaError_t launch_walk_fmt3(int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow_fmt3(int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2, uint32_t n_batches, cudaStream_t s);
+cudaError_t launch_walk_fmt4(int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow_fmt4(int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2, uint32_t n_batches, cudaStream_t s);
+cudaError_t launch_walk_fmt5(int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
+cudaError_t launch_slow_fmt5(int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2, uint32_t n_batches, cudaStream_t s);
+}

@@ -1,0 +1,202 @@
+// Per-thread body of the scan ("walk") kernel, written so that the identical code runs under the
+// host emulation (VG_HOST_EMU) in tests/ and inside the __global__ wrappers in scan_kernels.cu.
+//
+// One launch covers a contiguous window of W = n_threads * 2*half keys. Thread t owns the 2*half keys
+// [t*2H, (t+1)*2H) of the window, centred on C_t = (window_base + t*2H + H) * G, and derives them as
+// C_t +/- i*G (i = 1..H) with ONE field inversion for the whole batch (Montgomery's trick; the +/-
+// pair shares its inverse because x(i*G) = x(-i*G)). The same inversion also yields C_t + W*G, the
+// centre for the next window. This replaces the reference's `main` entry point
+// (src/shaders/search.wgsl:2-31: one Jacobian add + one 505-multiplication Fermat inversion per key)
+// and its host loop's per-key address/regex work (src/gpu.rs:1030-1093): digests are matched on the
+// device and only hits leave the chip.
+#pragma once
+#include "ec.cuh"
+#include "hash.cuh"
+#include "scan_types.h"
+
+template <int FMT>
+VG_DEV void vg_digest_of_point(uint32_t dg[VG_DIGEST_WORDS], const fe &x, const fe &y) {
+    VG_UNROLL for (int i = 5; i < VG_DIGEST_WORDS; i++) dg[i] = 0;
+    if (FMT == VG_FMT_P2PKH || FMT == VG_FMT_P2WPKH) {
+        hash160_pub33(dg, 2u + (y.v[0] & 1u), x);
+    } else if (FMT == VG_FMT_P2PKH_UNCOMPRESSED) {
+        hash160_pub65(dg, x, y);
+    } else if (FMT == VG_FMT_P2SH_P2WPKH) {
+        uint32_t h[5]; hash160_pub33(h, 2u + (y.v[0] & 1u), x); hash160_p2sh_script(dg, h);
+    } else if (FMT == VG_FMT_ETHEREUM) {
+        keccak_eth_address(dg, x, y);
+    } else {   // P2TR fast path yields the even-Y internal key x (as src/shaders/search_p2tr.wgsl:104-113)
+        VG_UNROLL for (int i = 0; i < 8; i++) dg[i] = vg_bswap(x.v[7 - i]);
+    }
+}
+
+VG_DEV bool vg_prefilter(const vg_matcher_dev &m, const uint32_t dg[VG_DIGEST_WORDS]) {
+    if (m.kind == VG_MATCH_ALL || m.kind == VG_MATCH_DFA) return true;
+    if (m.kind == VG_MATCH_EXACT) {
+        uint32_t d = 0;
+        for (int i = 0; i < m.exact_words; i++) d |= dg[i] ^ m.exact[i];
+        return d == 0;
+    }
+    uint32_t hi = vg_bswap(dg[0]), lo = vg_bswap(dg[1]);
+    bool hit = false;
+    for (int k = 0; k < m.n_intervals; k++) {
+        const uint32_t *iv = m.lo_hi[k];
+        bool ge = hi > iv[0] || (hi == iv[0] && lo >= iv[1]);
+        bool le = hi < iv[2] || (hi == iv[2] && lo <= iv[3]);
+        hit = hit || (ge && le);
+    }
+    return hit;
+}
+
+#ifdef VG_HOST_EMU
+static inline void vg_emit_hit(const vg_scan_params &P, bool is_hit, unsigned long long idx, const uint32_t dg[VG_DIGEST_WORDS]) {
+    if (!is_hit) return;
+    uint32_t slot = (*P.hit_count)++;
+    if (slot < P.hit_cap) {
+        P.hits[slot].idx_lo = (uint32_t)idx; P.hits[slot].idx_hi = (uint32_t)(idx >> 32);
+        for (int i = 0; i < VG_DIGEST_WORDS; i++) P.hits[slot].digest[i] = dg[i];
+    }
+}
+#else
+// warp-ballot compaction: one atomicAdd per warp that has hits; the count keeps growing past the
+// capacity so the host can detect overflow and rescan the window in smaller pieces.
+__device__ __forceinline__ void vg_emit_hit(const vg_scan_params &P, bool is_hit, unsigned long long idx, const uint32_t dg[VG_DIGEST_WORDS]) {
+    unsigned mask = __ballot_sync(0xffffffffu, is_hit);
+    if (mask == 0) return;
+    unsigned lane = threadIdx.x & 31u, leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(P.hit_count, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (is_hit) {
+        uint32_t slot = base + __popc(mask & ((1u << lane) - 1u));
+        if (slot < P.hit_cap) {
+            vg_hit_rec *h = P.hits + slot;
+            h->idx_lo = (uint32_t)idx; h->idx_hi = (uint32_t)(idx >> 32);
+            #pragma unroll
+            for (int i = 0; i < VG_DIGEST_WORDS; i++) h->digest[i] = dg[i];
+        }
+    }
+}
+#endif
+
+template <int FMT> VG_DEV bool vg_confirm(const vg_matcher_dev &m, const uint32_t dg[VG_DIGEST_WORDS]);
+
+template <int FMT, int MODE>
+VG_DEV void vg_process_point(const vg_scan_params &P, fe &x, fe &y, unsigned long long idx, bool valid) {
+    fe_canon(x); fe_canon(y);
+    uint32_t dg[VG_DIGEST_WORDS];
+    vg_digest_of_point<FMT>(dg, x, y);
+    valid = valid && idx < P.limit;
+    if (MODE == VG_MODE_DUMP) {
+        if (valid) {
+            uint8_t *o = P.dump + idx * P.dump_stride;
+            for (uint32_t b = 0; b < P.dump_stride; b++) o[b] = (uint8_t)(dg[b >> 2] >> (8 * (b & 3)));
+        }
+    } else {
+        bool hit = valid && vg_prefilter(P.m, dg);
+        if (hit && (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa)) hit = vg_confirm<FMT>(P.m, dg);
+        vg_emit_hit(P, hit, idx, dg);
+    }
+}
+
+#define VG_LOAD_FE(dst, base, stride_words) { VG_UNROLL for (int _l = 0; _l < 8; _l++) (dst).v[_l] = (base)[(size_t)_l * (stride_words)]; }
+#define VG_STORE_FE(base, stride_words, src) { VG_UNROLL for (int _l = 0; _l < 8; _l++) (base)[(size_t)_l * (stride_words)] = (src).v[_l]; }
+
+// gtab: pointer to the i*G table (shared memory in the kernel), entry i-1 = 16 words
+template <int FMT, int MODE>
+VG_DEV void vg_walk_thread(const vg_scan_params &P, const uint32_t *gtab, uint32_t tid) {
+    const uint32_t T = P.n_threads, H = P.half;
+    fe cx, cy, sx, sy;
+    VG_LOAD_FE(cx, P.centers + tid, T);
+    VG_LOAD_FE(cy, P.centers + (size_t)8 * T + tid, T);
+    VG_UNROLL for (int l = 0; l < 8; l++) { sx.v[l] = P.stride_pt[l]; sy.v[l] = P.stride_pt[8 + l]; }
+    bool degenerate = fe_is_zero_raw(cx) && fe_is_zero_raw(cy);
+
+    // forward pass: prefix products of dx_0 = Sx - Cx, dx_i = x(i*G) - Cx
+    uint32_t *scr = P.scratch + tid;
+    fe prod, dx;
+    fe_sub(prod, sx, cx);
+    if (fe_is_zero_raw(prod)) { degenerate = true; fe_set_one(prod); }
+    VG_STORE_FE(scr, T, prod);
+    for (uint32_t i = 1; i <= H; i++) {
+        const uint32_t *g = gtab + (size_t)(i - 1) * 16;
+        fe gx; VG_UNROLL for (int l = 0; l < 8; l++) gx.v[l] = g[l];
+        fe_sub(dx, gx, cx);
+        if (fe_is_zero_raw(dx)) { degenerate = true; fe_set_one(dx); }
+        fe_mul(prod, prod, dx);
+        VG_STORE_FE(scr + (size_t)i * 8 * T, T, prod);
+    }
+    fe inv;
+    fe_inv(inv, prod);
+
+    const unsigned long long idx_c = (unsigned long long)tid * (2ull * H) + H;
+    // backward pass: peel one inverse per step, derive both neighbours, hash, match
+    for (uint32_t i = H; i >= 1; i--) {
+        const uint32_t *g = gtab + (size_t)(i - 1) * 16;
+        fe gx, gy, pre, inv_i;
+        VG_UNROLL for (int l = 0; l < 8; l++) { gx.v[l] = g[l]; gy.v[l] = g[8 + l]; }
+        VG_LOAD_FE(pre, scr + (size_t)(i - 1) * 8 * T, T);
+        fe_mul(inv_i, inv, pre);
+        fe_sub(dx, gx, cx);
+        if (fe_is_zero_raw(dx)) fe_set_one(dx);
+        fe_mul(inv, inv, dx);
+#ifndef VG_HOST_EMU
+        #pragma unroll 1
+#endif
+        for (int side = (i == H ? 1 : 0); side < 2; side++) {
+            fe x3, y3, by;
+            if (side) fe_neg(by, gy); else by = gy;
+            affine_add_inv(x3, y3, cx, cy, gx, by, inv_i);
+            unsigned long long idx = side ? idx_c - i : idx_c + i;
+            vg_process_point<FMT, MODE>(P, x3, y3, idx, !degenerate);
+        }
+    }
+    {   // the centre itself
+        fe x3 = cx, y3 = cy;
+        vg_process_point<FMT, MODE>(P, x3, y3, idx_c, !degenerate);
+    }
+    // next centre: C + W*G, with inv = 1/(Sx - Cx)
+    fe nx, ny;
+    affine_add_inv(nx, ny, cx, cy, sx, sy, inv);
+    fe_canon(nx); fe_canon(ny);
+    if (degenerate) {
+        fe_set_zero(nx); fe_set_zero(ny);
+#ifdef VG_HOST_EMU
+        uint32_t slot = (*P.degen_count)++;
+#else
+        uint32_t slot = atomicAdd(P.degen_count, 1u);
+#endif
+        if (slot < P.degen_cap) P.degen_list[slot] = tid;
+    }
+    VG_STORE_FE(P.centers + tid, T, nx);
+    VG_STORE_FE(P.centers + (size_t)8 * T + tid, T, ny);
+}
+
+// ---- cold-path thread bodies ----
+// pow2[i] = 2^i * G for i = 0..255, built serially by one thread at context creation
+VG_DEV void vg_build_pow2(uint32_t *pow2, const uint32_t gxy[16]) {
+    gej_t p; fe x, y;
+    VG_UNROLL for (int l = 0; l < 8; l++) { x.v[l] = gxy[l]; y.v[l] = gxy[8 + l]; }
+    for (int i = 0; i < 256; i++) {
+        for (int l = 0; l < 8; l++) { pow2[i * 16 + l] = x.v[l]; pow2[i * 16 + 8 + l] = y.v[l]; }
+        p.x = x; p.y = y; fe_set_one(p.z); p.inf = false;
+        gej_t d; gej_double(d, p);
+        gej_to_affine(x, y, d);
+    }
+}
+// affine point of scalar base + mul*tid + add, stored limb-major at column tid of out[16][n]; zeros if invalid
+VG_DEV void vg_point_of_scalar(uint32_t *out, uint32_t n, uint32_t col, const uint32_t k[8], const uint32_t *pow2) {
+    fe x, y;
+    bool ok = scalar_is_valid(k) && scalar_mul_pow2(x, y, k, pow2);
+    if (!ok) { fe_set_zero(x); fe_set_zero(y); }
+    VG_STORE_FE(out + col, n, x);
+    VG_STORE_FE(out + (size_t)8 * n + col, n, y);
+}
+// slow generic path for one key: full scalar multiplication, every edge case handled
+template <int FMT, int MODE>
+VG_DEV void vg_slow_key(const vg_scan_params &P, const uint32_t k[8], unsigned long long idx, const uint32_t *pow2) {
+    fe x, y;
+    bool ok = scalar_is_valid(k) && scalar_mul_pow2(x, y, k, pow2);
+    if (!ok) { fe_set_zero(x); fe_set_zero(y); }
+    vg_process_point<FMT, MODE>(P, x, y, idx, ok);
+}

@@ -1,0 +1,43 @@
+// Plain-C types shared by the device code (scan_core.cuh) and the host engine (engine.cpp).
+#pragma once
+#include <stdint.h>
+
+enum { VG_FMT_P2PKH = 0, VG_FMT_P2PKH_UNCOMPRESSED = 1, VG_FMT_P2WPKH = 2, VG_FMT_P2SH_P2WPKH = 3, VG_FMT_P2TR = 4, VG_FMT_ETHEREUM = 5 };
+enum { VG_MATCH_ALL = 0, VG_MATCH_INTERVALS = 1, VG_MATCH_EXACT = 2, VG_MATCH_DFA = 3 };
+enum { VG_MODE_MATCH = 0, VG_MODE_DUMP = 1 };
+
+#define VG_MAX_INTERVALS 32
+#define VG_DIGEST_WORDS 8
+
+struct vg_hit_rec {          // 40 bytes
+    uint32_t idx_lo, idx_hi; // key index inside the window
+    uint32_t digest[VG_DIGEST_WORDS];   // digest bytes as little-endian words (byte 4i+j = byte j of digest[i])
+};
+struct vg_dfa_dev {
+    const uint16_t *table;   // [n_states][n_classes] next state
+    const uint8_t *accept;   // [n_states] bit0: accepting if input ends here
+    uint32_t n_states, n_classes, start;
+    uint8_t class_of[128];   // ASCII -> class
+};
+struct vg_matcher_dev {
+    int kind;
+    int n_intervals;
+    uint32_t lo_hi[VG_MAX_INTERVALS][4];   // {lo_hi32, lo_lo32, hi_hi32, hi_lo32}: inclusive range of the first 8 digest bytes (big-endian)
+    uint32_t exact[VG_DIGEST_WORDS];       // little-endian words, as produced by the hashes
+    int exact_words;
+    int confirm_dfa;                       // run the DFA on candidates that pass the prefilter
+    vg_dfa_dev dfa;
+};
+struct vg_scan_params {
+    uint32_t n_threads, half;
+    uint32_t *centers;        // [16][n_threads]: x limbs 0..7 then y limbs 0..7 (canonical); all-zero = no valid centre
+    uint32_t *scratch;        // [(half+1)][8][n_threads] prefix products
+    const uint32_t *gtab;     // [half][16]: (i+1)*G affine canonical, x limbs then y limbs
+    uint32_t stride_pt[16];   // W*G affine canonical
+    unsigned long long limit; // window keys with index < limit are inside the scan range
+    vg_hit_rec *hits; uint32_t *hit_count; uint32_t hit_cap;
+    uint32_t *degen_list; uint32_t *degen_count; uint32_t degen_cap;
+    uint8_t *dump; uint32_t dump_stride;   // VG_MODE_DUMP: digest bytes per key index
+    vg_matcher_dev m;
+};
+
