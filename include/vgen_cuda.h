@@ -1,0 +1,104 @@
+/* libvgen_cuda — C ABI of the B200 (sm_100a) keygen-and-match engine.
+ *
+ * Drop-in boundary for vgen's GPU scan path: these entry points are what a new src/gpu.rs binds instead
+ * of wgpu (see INTEGRATION.md for the Rust `extern "C"` block and the ctypes binding used by tests/).
+ * Plain pointers and sizes only; no CUDA or torch types in any signature. All functions return
+ * VGEN_OK (0) or a negative error class; vgen_cuda_last_error() gives the message. Nothing throws or
+ * aborts across the boundary. One scan at a time per context.
+ *
+ * Reference interface replaced (file:line in oritwoen/vgen v0.3.0):
+ *   GpuRunner::new                    src/gpu.rs:138-533   -> vgen_cuda_create
+ *   GpuRunner::{device_name,backend}  src/gpu.rs:128-136   -> vgen_cuda_device_name
+ *   GpuRunner::generate_batch         src/gpu.rs:660-665   -> vgen_cuda_hash160_batch
+ *   GpuRunner::dispatch/await_result  src/gpu.rs:535-658   -> (internal; two windows in flight per GPU)
+ *   scan_gpu_with_runner / scan_gpu   src/gpu.rs:920-1166  -> vgen_cuda_set_pattern + vgen_cuda_scan
+ *   Pattern::new / Pattern::matches   src/pattern.rs:21-45 -> vgen_cuda_set_pattern / vgen_pattern_is_match
+ *   hash160 -> address string, WIF    src/gpu.rs:1034-1060,1080; src/address.rs:92-151 -> vgen_format_address / vgen_format_wif
+ */
+#ifndef VGEN_CUDA_H
+#define VGEN_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VGEN_OK 0
+#define VGEN_ERR_INVALID_ARG (-1)
+#define VGEN_ERR_CUDA (-2)       /* a CUDA call failed, or no sm_100 device */
+#define VGEN_ERR_PATTERN (-3)    /* empty / invalid / unsupported regex (src/pattern.rs:22-33) */
+#define VGEN_ERR_RANGE (-4)      /* end < start */
+#define VGEN_ERR_BUFFER (-5)     /* caller buffer too small */
+
+/* AddressFormat (src/address.rs:11-46) */
+enum vgen_format {
+    VGEN_P2PKH = 0, VGEN_P2PKH_UNCOMPRESSED = 1, VGEN_P2WPKH = 2, VGEN_P2SH_P2WPKH = 3, VGEN_P2TR = 4, VGEN_ETHEREUM = 5
+};
+
+typedef struct vgen_ctx vgen_ctx;
+
+typedef struct vgen_hit {
+    uint8_t key_be[32];      /* secret key, big-endian */
+    uint8_t digest[32];      /* hash160 / Ethereum address bytes (20) or tweaked x-only key (32) */
+    uint32_t digest_len;
+    uint32_t device;         /* lane (index into the device list given at create) that found it */
+} vgen_hit;
+
+/* progress callback: cumulative number of valid keys tested so far; called on the calling thread
+ * (ProgressCallback, src/scanner.rs:71; src/gpu.rs:1107-1109) */
+typedef void (*vgen_progress_fn)(uint64_t keys_scanned, void *user);
+
+int vgen_cuda_device_count(void);
+int vgen_cuda_device_name(int device, char *buf, size_t len);
+
+/* devices == NULL or n_devices == 0 selects device 0. keys_per_launch_hint mirrors ScanConfig.gpu_batch_size
+ * (src/scanner.rs:40, default 524,288 in the reference); 0 = two resident CTAs per SM (~77.6 M keys / launch). */
+int vgen_cuda_create(const int *devices, int n_devices, uint32_t keys_per_launch_hint, vgen_ctx **out);
+void vgen_cuda_destroy(vgen_ctx *ctx);
+/* message of the last error on this context (ctx == NULL: last error of a failed create on this thread) */
+const char *vgen_cuda_last_error(const vgen_ctx *ctx);
+
+/* Pattern::new(pattern, case_insensitive) + lowering for `format`. */
+int vgen_cuda_set_pattern(vgen_ctx *ctx, int format, const char *pattern, int case_insensitive);
+/* how the current pattern was lowered: "intervals" | "exact" | "dfa" | "all" | "none" */
+const char *vgen_cuda_matcher_kind(const vgen_ctx *ctx);
+
+/* This context handles global lanes [shard_index*n_devices, (shard_index+1)*n_devices) of shard_count*n_devices:
+ * lets one process per GPU (torchrun) split a range with disjoint start scalars and a common stride. */
+int vgen_cuda_set_shard(vgen_ctx *ctx, uint32_t shard_index, uint32_t shard_count);
+/* run lane `lane` on a caller-owned cudaStream_t (passed as void*), e.g. torch's current stream */
+int vgen_cuda_set_stream(vgen_ctx *ctx, int lane, void *cuda_stream);
+
+/* Scan [start, end] inclusive (end == NULL: up to n-1) with the current pattern. Scalars 0 and >= n are
+ * skipped and not counted (src/scanner.rs:294-295). Hits are written in ascending key order, at most
+ * min(max_hits, hits_cap) of them (max_hits == 0: unlimited); *n_hits is the number written.
+ * `stop` (may be NULL) is polled after every window; progress (may be NULL) is called after every window. */
+int vgen_cuda_scan(vgen_ctx *ctx, const uint8_t start_be[32], const uint8_t *end_be, uint64_t max_hits,
+                   const volatile int32_t *stop, vgen_progress_fn progress, void *user,
+                   vgen_hit *hits_out, uint64_t hits_cap, uint64_t *n_hits, uint64_t *keys_scanned);
+
+/* generate_batch (src/gpu.rs:660): hash160 of the compressed public key of n sequential scalars, 20 bytes
+ * each; zeros for invalid scalars. */
+int vgen_cuda_hash160_batch(vgen_ctx *ctx, const uint8_t start_be[32], uint64_t n, uint8_t *out20);
+/* same for any format's digest, `stride` bytes per key (20, or 32 for P2TR's internal key) */
+int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride);
+
+/* Device-resident timing for bench.py: centres set up untimed, then n_windows full-size windows of the current
+ * pattern timed with CUDA events on lane 0's stream. */
+int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t n_windows, float *ms, uint64_t *keys, uint64_t *launches);
+/* kernel launches issued by this context so far; keys per full-size window */
+uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx);
+uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx);
+
+/* Host-side string work the reference does per key and this library does per hit. Return the string length. */
+int vgen_format_address(int format, const uint8_t *digest, char *out, size_t cap);
+int vgen_format_wif(int format, const uint8_t key_be[32], char *out, size_t cap);
+/* Pattern::new error check and Pattern::matches on an arbitrary string (1 / 0, <0 on a bad pattern) */
+int vgen_pattern_check(const char *pattern, int case_insensitive, char *err, size_t cap);
+int vgen_pattern_is_match(const char *pattern, int case_insensitive, const char *text);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

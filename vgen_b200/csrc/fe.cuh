@@ -34,7 +34,7 @@ static inline uint32_t vg_mad_hi_cc(uint32_t a, uint32_t b, uint32_t c, uint32_t
 #define VG_UNROLL
 #else
 #define VG_DEV __device__ __forceinline__
-#define VG_COLD __device__ __noinline__
+#define VG_COLD static __device__ __noinline__
 #define ADD_CC(r, a, b) asm volatile("add.cc.u32 %0,%1,%2;" : "=r"(r) : "r"(a), "r"(b))
 #define ADDC_CC(r, a, b) asm volatile("addc.cc.u32 %0,%1,%2;" : "=r"(r) : "r"(a), "r"(b))
 #define ADDC(r, a, b) asm volatile("addc.u32 %0,%1,%2;" : "=r"(r) : "r"(a), "r"(b))

@@ -1,0 +1,147 @@
+// extern "C" surface of libvgen_cuda.so (include/vgen_cuda.h) over vg::Engine.
+#include "../../../include/vgen_cuda.h"
+#include "engine.h"
+#include <string.h>
+#include <new>
+
+struct vgen_ctx {
+    vg::Engine engine;
+    std::string last_error;
+};
+static thread_local std::string g_create_error;
+
+static int fail(vgen_ctx *ctx, int code, const std::string &msg) {
+    if (ctx) ctx->last_error = msg; else g_create_error = msg;
+    return code;
+}
+static int copy_out(const std::string &s, char *out, size_t cap) {
+    if (!out || cap < s.size() + 1) return VGEN_ERR_BUFFER;
+    memcpy(out, s.c_str(), s.size() + 1);
+    return (int)s.size();
+}
+
+extern "C" {
+
+int vgen_cuda_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+int vgen_cuda_device_name(int device, char *buf, size_t len) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, device) != cudaSuccess) return VGEN_ERR_CUDA;
+    return copy_out(p.name, buf, len) < 0 ? VGEN_ERR_BUFFER : VGEN_OK;
+}
+int vgen_cuda_create(const int *devices, int n_devices, uint32_t hint, vgen_ctx **out) {
+    if (!out) return fail(nullptr, VGEN_ERR_INVALID_ARG, "out is NULL");
+    *out = nullptr;
+    vgen_ctx *ctx = new (std::nothrow) vgen_ctx;
+    if (!ctx) return fail(nullptr, VGEN_ERR_INVALID_ARG, "out of memory");
+    std::string err;
+    try {
+        if (!ctx->engine.create(devices, n_devices, hint, err)) { delete ctx; return fail(nullptr, VGEN_ERR_CUDA, err); }
+    } catch (const std::exception &e) { delete ctx; return fail(nullptr, VGEN_ERR_CUDA, e.what()); }
+    *out = ctx;
+    return VGEN_OK;
+}
+void vgen_cuda_destroy(vgen_ctx *ctx) { delete ctx; }
+const char *vgen_cuda_last_error(const vgen_ctx *ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
+
+int vgen_cuda_set_pattern(vgen_ctx *ctx, int format, const char *pattern, int ci) {
+    if (!ctx || !pattern) return VGEN_ERR_INVALID_ARG;
+    if (format < 0 || format > 5) return fail(ctx, VGEN_ERR_INVALID_ARG, "invalid address format");
+    std::string err;
+    try {
+        vg::LoweredPattern probe;
+        if (!vg::lower_pattern(format, pattern, ci != 0, probe, err)) return fail(ctx, VGEN_ERR_PATTERN, err);
+        if (!ctx->engine.set_pattern(format, pattern, ci != 0, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+    } catch (const std::exception &e) { return fail(ctx, VGEN_ERR_PATTERN, e.what()); }
+    return VGEN_OK;
+}
+const char *vgen_cuda_matcher_kind(const vgen_ctx *ctx) {
+    if (!ctx || !ctx->engine.has_pattern()) return "";
+    return ctx->engine.pattern().kind_name.c_str();
+}
+int vgen_cuda_set_shard(vgen_ctx *ctx, uint32_t index, uint32_t count) {
+    if (!ctx) return VGEN_ERR_INVALID_ARG;
+    std::string err;
+    if (!ctx->engine.set_shard(index, count, err)) return fail(ctx, VGEN_ERR_INVALID_ARG, err);
+    return VGEN_OK;
+}
+int vgen_cuda_set_stream(vgen_ctx *ctx, int lane, void *stream) {
+    if (!ctx) return VGEN_ERR_INVALID_ARG;
+    std::string err;
+    if (!ctx->engine.set_stream(lane, (cudaStream_t)stream, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+    return VGEN_OK;
+}
+int vgen_cuda_scan(vgen_ctx *ctx, const uint8_t start_be[32], const uint8_t *end_be, uint64_t max_hits,
+                   const volatile int32_t *stop, vgen_progress_fn progress, void *user,
+                   vgen_hit *hits_out, uint64_t hits_cap, uint64_t *n_hits, uint64_t *keys_scanned) {
+    if (!ctx || !start_be || !n_hits || !keys_scanned || (!hits_out && hits_cap)) return VGEN_ERR_INVALID_ARG;
+    *n_hits = 0; *keys_scanned = 0;
+    std::string err;
+    try {
+        vg::U256 start = vg::U256::from_be(start_be), end;
+        if (end_be) { end = vg::U256::from_be(end_be); if (end < start) return fail(ctx, VGEN_ERR_RANGE, "range end is below range start"); }
+        uint64_t want = max_hits ? std::min<uint64_t>(max_hits, hits_cap) : hits_cap;
+        std::vector<vg::Hit> hits;
+        vg::Engine::Progress cb;
+        if (progress) cb = [&](uint64_t k) { progress(k, user); };
+        if (!ctx->engine.scan(start, end_be ? &end : nullptr, want, stop, cb, hits, *keys_scanned, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+        uint64_t n = std::min<uint64_t>(hits.size(), hits_cap);
+        for (uint64_t i = 0; i < n; i++) {
+            hits[i].key.to_be(hits_out[i].key_be);
+            memcpy(hits_out[i].digest, hits[i].digest, 32);
+            hits_out[i].digest_len = hits[i].digest_len; hits_out[i].device = hits[i].lane;
+        }
+        *n_hits = n;
+    } catch (const std::exception &e) { return fail(ctx, VGEN_ERR_CUDA, e.what()); }
+    return VGEN_OK;
+}
+int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride) {
+    if (!ctx || !start_be || (!out && n)) return VGEN_ERR_INVALID_ARG;
+    std::string err;
+    try {
+        if (!ctx->engine.digest_batch(format, vg::U256::from_be(start_be), n, out, stride, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+    } catch (const std::exception &e) { return fail(ctx, VGEN_ERR_CUDA, e.what()); }
+    return VGEN_OK;
+}
+int vgen_cuda_hash160_batch(vgen_ctx *ctx, const uint8_t start_be[32], uint64_t n, uint8_t *out20) {
+    return vgen_cuda_digest_batch(ctx, VGEN_P2PKH, start_be, n, out20, 20);
+}
+int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t n_windows, float *ms, uint64_t *keys, uint64_t *launches) {
+    if (!ctx || !start_be || !ms || !keys || !launches) return VGEN_ERR_INVALID_ARG;
+    std::string err;
+    if (!ctx->engine.bench_resident(vg::U256::from_be(start_be), n_windows, *ms, *keys, *launches, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+    return VGEN_OK;
+}
+uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.launches : 0; }
+uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx) { return ctx ? ctx->engine.levels().back().window : 0; }
+
+int vgen_format_address(int format, const uint8_t *digest, char *out, size_t cap) {
+    if (!digest || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;
+    return copy_out(vg::format_address(format, digest), out, cap);
+}
+int vgen_format_wif(int format, const uint8_t key_be[32], char *out, size_t cap) {
+    if (!key_be || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;
+    return copy_out(vg::format_wif(format, key_be), out, cap);
+}
+int vgen_pattern_check(const char *pattern, int ci, char *errbuf, size_t cap) {
+    if (!pattern) return VGEN_ERR_INVALID_ARG;
+    vg::Dfa d; vg::PatternInfo info; std::string err;
+    try {
+        if (vg::compile_pattern(pattern, ci != 0, d, info, err)) return VGEN_OK;
+    } catch (const std::exception &e) { err = e.what(); }
+    if (errbuf && cap) { strncpy(errbuf, err.c_str(), cap - 1); errbuf[cap - 1] = 0; }
+    return VGEN_ERR_PATTERN;
+}
+int vgen_pattern_is_match(const char *pattern, int ci, const char *text) {
+    if (!pattern || !text) return VGEN_ERR_INVALID_ARG;
+    vg::Dfa d; vg::PatternInfo info; std::string err;
+    try {
+        if (!vg::compile_pattern(pattern, ci != 0, d, info, err)) return VGEN_ERR_PATTERN;
+    } catch (const std::exception &) { return VGEN_ERR_PATTERN; }
+    return d.match(text, strlen(text)) ? 1 : 0;
+}
+
+}  // extern "C"
