@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the B200 key-scan hot path (Mkeys/s, P2PKH ^1Cat prefix scan) with its integer-issue
+roofline, the end-to-end figure through the public API, and the CPU baseline.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            own arm (one process per GPU under torchrun for N > 1)
+  python bench.py --impl reference [--gpus N] [--steps K] ...    the reference's CPU scan path (oracle port) on host cores
+
+A step = one pass of the scan path over `--windows-per-step` full launch windows per GPU (fixed synthetic key range
+from 2^64; keys are a counter, nothing is loaded). Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "Mkeys/s P2PKH ^1Cat scan"
+START = 1 << 64
+# algorithmic work per key, 32-bit integer instruction slots (DESIGN.md "Roofline"; SURVEY.md 8d, +/- variant, c_w = 1):
+#   EC 3.5M + 1S = 300.5 limb products + ~300 carry/add slots, SHA-256 ~1400, RIPEMD-160 ~975, matcher ~15
+W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed": 4450, "ethereum": 5220}
+HBM_BYTES_PER_KEY = 32          # prefix-product scratch: 32 B written + 32 B read per +/- key pair
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(",")]))
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        rows = [r for t, r in self.rows if t0 <= t <= t1 and len(r) >= 8] or [r for _, r in self.rows if len(r) >= 8]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"], "samples": 0}
+        sm = sorted(float(r[1]) for r in rows)
+        reasons = []
+        for i, name in ((4, "hw_slowdown"), (5, "hw_thermal_slowdown"), (6, "sw_thermal_slowdown"), (7, "sw_power_cap")):
+            if any(r[i].lower().startswith("active") for r in rows):
+                reasons.append(name)
+        pw = [float(r[3]) for r in rows if r[3].replace(".", "", 1).isdigit()]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][2]), "reasons": reasons, "samples": len(rows),
+                "power_w_max": max(pw) if pw else None}
+
+
+def load_json(path):
+    try:
+        with open(path) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return None
+
+
+def cpu_scan_sample(fmt, pattern, threads, target_s):
+    """Times the oracle's scan_range_cpu port on a bounded sample of the same workload (same start, format, pattern)."""
+    import oracle
+    n = 1 << 14
+    keys, ops, el = oracle.scan_range(fmt, pattern, START, n, threads=threads)
+    rate = ops / max(el, 1e-6)
+    n = max(1 << 14, min(1 << 26, int(rate * target_s)))
+    keys, ops, el = oracle.scan_range(fmt, pattern, START, n, threads=threads)
+    return ops, el, len(keys)
+
+
+def run_reference(args):
+    """Reference arm: the reference's own CPU implementation of the path (scan_range_cpu + AddressGenerator::generate,
+    src/scanner.rs:211-330) as restated by oracle/ (the Rust reference cannot be built here: no cargo/rustc), on all host threads."""
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    import oracle
+    oracle.lib()
+    per_step_s = 3.0
+    for _ in range(max(args.warmup, 1)):
+        cpu_scan_sample(args.format, args.pattern, threads, 0.5)
+    tot_ops, tot_el, sample_keys = 0, 0.0, 0
+    for _ in range(args.steps):
+        ops, el, _ = cpu_scan_sample(args.format, args.pattern, threads, per_step_s)
+        tot_ops += ops
+        tot_el += el
+        sample_keys = ops
+    val = tot_ops / tot_el / 1e6
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "Mkeys/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": tot_el / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+        "data": "synthetic", "config": workload_config(args, None),
+        "cpu_baseline": {"value": val, "unit": "Mkeys/s", "cores": threads, "kind": "port",
+                         "sample": "%d consecutive keys from 2^64 per step (~%.0f s), %s %s, %d steps" % (sample_keys, per_step_s, args.format, args.pattern, args.steps)},
+        "e2e": {"value": val, "unit": "Mkeys/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "oracle port of vgen's rayon CPU scanner (one independent k*G per key, Base58Check + regex per key); README.md:175 quotes 0.05-0.2 Mkeys/s",
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, runner):
+    cfg = {"workload": "BASELINE configs[1] shape: P2PKH compressed prefix scan (hash160 interval-compare path), pattern %s, fixed key range from 2^64" % args.pattern,
+           "format": args.format, "pattern": args.pattern, "start": "2^64", "windows_per_step": args.windows_per_step,
+           "parallelism": "keyspace shards, %d rank(s), no collective" % args.gpus,
+           "l2": "per-launch working set (prefix-product scratch, 1.24 GB) exceeds the 126 MB L2; no flush needed"}
+    if runner is not None:
+        cfg["keys_per_window"] = runner.batch_size
+        cfg["keys_per_step_per_gpu"] = runner.batch_size * args.windows_per_step
+        cfg["matcher"] = runner.matcher_kind()
+    return cfg
+
+
+def run_own(args):
+    import torch
+    import torch.distributed as dist
+    import vgen_b200 as vg
+
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the scan path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    runner = vg.GpuRunner(devices=[local], shard=(rank, world))
+    fmt = vg.AddressFormat.parse(args.format)
+    pat = vg.Pattern(args.pattern)
+    runner.set_pattern(pat, fmt)
+    wps, K, W = args.windows_per_step, args.steps, args.warmup
+    step_keys = runner.batch_size * wps                 # per GPU
+
+    # ---- device-resident arm: centres already in HBM when the timed region starts; CUDA events on the launch stream
+    runner.bench_resident(START, max(W, 3) * wps)       # warm-up
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    barrier()
+    l0 = runner.launch_count()
+    t0 = time.perf_counter()
+    ms, keys, launches = runner.bench_resident(START + (1 << 40), K * wps)
+    barrier()
+    t1 = time.perf_counter()
+    gpu_launches = runner.launch_count() - l0 - 1        # minus the untimed centre set-up launch
+    ms_max = allmax(ms)
+    total_keys = allsum(keys)
+    value = total_keys / (ms_max * 1e-3) / 1e6
+    clocks = sampler.summary(t0, t1)
+
+    # ---- end-to-end arm: the public call (scan_gpu_with_runner) with host-side start/end scalars, centre set-up,
+    # launch parameters, hit records and counters crossing PCIe inside the timed region
+    span = step_keys * world
+    cfg0 = vg.ScanConfig(format=fmt, count=0, start=START + (1 << 44), end=START + (1 << 44) + span - 1)
+    vg.scan_gpu_with_runner(pat, cfg0, None, None, runner)          # warm-up
+    io0 = runner.io_bytes()
+    barrier()
+    e0 = time.perf_counter()
+    e_keys, e_hits = 0, 0
+    for s in range(K):
+        a = START + (1 << 45) + s * span
+        res = vg.scan_gpu_with_runner(pat, vg.ScanConfig(format=fmt, count=0, start=a, end=a + span - 1), None, None, runner)
+        e_keys += res.operations
+        e_hits += len(res.matches)
+    barrier()
+    e_ms = allmax((time.perf_counter() - e0) * 1e3)
+    sampler.stop()
+    io1 = runner.io_bytes()
+    e_total = allsum(e_keys)
+    e_hits_total = allsum(e_hits)
+    e2e = {"value": e_total / (e_ms * 1e-3) / 1e6, "unit": "Mkeys/s",
+           "h2d_bytes_per_step": (io1[0] - io0[0]) // K, "d2h_bytes_per_step": (io1[1] - io0[1]) // K,
+           "ms_per_step": e_ms / K, "hits_per_step": e_hits_total / K,
+           "api": "vgen_b200.scan_gpu_with_runner -> vgen_cuda_scan (host scalars in, confirmed hit records out)"}
+
+    # ---- roofline of the walk kernel (the only kernel in the timed region): integer issue, not HBM / tensor
+    peaks = load_json(os.path.join(ROOT, "MEASURED_PEAKS.json")) or {}
+    int_peaks = load_json(os.path.join(ROOT, "profiles", "peak_int.json")) or {}
+    ncu = load_json(os.path.join(ROOT, "profiles", "walk_kernel_ncu.json")) or {}
+    sm_max = clocks.get("sm_max_mhz") or peaks.get("sm_max_mhz") or 1965.0
+    sm_now = clocks.get("sm_mhz") or sm_max
+    w_int = W_INT.get(args.format, 3050)
+    keys_per_gpu_s = keys / (ms * 1e-3)
+    achieved = keys_per_gpu_s * w_int / 1e12
+    nominal_peak = 148 * 64 * sm_max * 1e6 / 1e12
+    peak = int_peaks.get("imad") or nominal_peak
+    roofline = {"bound": "int32-issue", "achieved": achieved, "peak": peak, "unit": "Tinst/s", "frac": achieved / peak,
+                "peak_source": "measured by peak_bench (profiles/peak_int.json), pure IMAD on 148 SMs" if int_peaks.get("imad") else "nominal 148 SMs x 64 lanes x max SM clock (no peak_bench record yet)",
+                "work_per_key_inst": w_int, "keys_per_launch": runner.batch_size, "launch_ms": ms / (K * wps),
+                "frac_at_sampled_clock": achieved / (148 * 64 * sm_now * 1e6 / 1e12),
+                "executed_inst_per_key_ncu": ncu.get("thread_inst_per_key"),
+                "traffic": ncu.get("dram_bytes_per_launch"),
+                "hbm": {"achieved": keys_per_gpu_s * HBM_BYTES_PER_KEY / 1e9, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
+                        "frac": (keys_per_gpu_s * HBM_BYTES_PER_KEY / 1e9) / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
+                        "peak_source": "of measured (MEASURED_PEAKS.json)" if peaks.get("hbm_gbs") else "absent"}}
+
+    line = {"metric": METRIC, "value": value, "unit": "Mkeys/s", "n_gpus": world, "steps": K, "warmup": max(W, 3), "ms_per_step": ms_max / K,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": workload_config(args, runner), "clocks": clocks, "e2e": e2e, "gpu_launches": int(gpu_launches), "roofline": roofline,
+            "device": runner.device_name}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        ops, el, nh = cpu_scan_sample(args.format, args.pattern, threads, 12.0)
+        line["cpu_baseline"] = {"value": ops / el / 1e6, "unit": "Mkeys/s", "cores": threads, "kind": "port",
+                                "sample": "first %d keys of the same range (from 2^64), %s %s, %.1f s, %d matches" % (ops, args.format, args.pattern, el, nh)}
+    runner.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--format", default="p2pkh")
+    ap.add_argument("--pattern", default="^1Cat")
+    ap.add_argument("--windows-per-step", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = env_int("WORLD_SIZE", 1)
+    if args.gpus > 1 and world == 1:
+        # convenience: re-launch under torchrun, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
+               "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    return run_own(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -90,6 +90,8 @@ int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t
 /* kernel launches issued by this context so far; keys per full-size window */
 uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx);
 uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx);
+/* bytes the scans of this context copied host->device (start scalars, launch parameters) and device->host (counters, hit records) */
+void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h);
 
 /* Host-side string work the reference does per key and this library does per hit. Return the string length. */
 int vgen_format_address(int format, const uint8_t *digest, char *out, size_t cap);
@@ -97,6 +99,10 @@ int vgen_format_wif(int format, const uint8_t key_be[32], char *out, size_t cap)
 /* Pattern::new error check and Pattern::matches on an arbitrary string (1 / 0, <0 on a bad pattern) */
 int vgen_pattern_check(const char *pattern, int case_insensitive, char *err, size_t cap);
 int vgen_pattern_is_match(const char *pattern, int case_insensitive, const char *text);
+/* How (format, pattern) is lowered for the device, without touching a GPU. Writes
+ * "<kind>[;<lo16hex>-<hi16hex>]*[;exact=<hex>]" (intervals over the leading 64 digest bits, inclusive);
+ * returns the string length. kind as vgen_cuda_matcher_kind. */
+int vgen_pattern_lowering(int format, const char *pattern, int case_insensitive, char *out, size_t cap);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,184 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA scan path, called through the C ABI, against the CPU oracle.
+Bit-exact: every digest byte of generate_batch, and identical (key, address) match sets for the scan."""
+import ctypes as C
+import hashlib
+import random
+
+import pytest
+
+import oracle
+import vgen_b200 as vg
+
+pytestmark = pytest.mark.gpu
+N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
+FORMATS = ["p2pkh", "p2pkh-uncompressed", "p2wpkh", "p2sh-p2wpkh", "ethereum"]
+
+
+@pytest.fixture(scope="module")
+def runner():
+    r = vg.GpuRunner()
+    yield r
+    r.close()
+
+
+@pytest.fixture(scope="module")
+def small_runner():
+    # reference-sized batches (DEFAULT_BATCH_SIZE = 524,288 keys per launch, src/gpu.rs:83)
+    r = vg.GpuRunner(vg.DEFAULT_BATCH_SIZE)
+    yield r
+    r.close()
+
+
+def test_library_is_the_cuda_one(runner):
+    assert "B200" in runner.device_name or runner.device_name
+    assert runner.backend() == vg.GpuBackend.Cuda
+    assert runner.batch_size % 1024 == 0
+
+
+def test_generate_batch_golden(runner, golden):
+    for r in golden["runs"]:
+        got = runner.generate_batch(int(r["start"], 16), len(r["hash160"]))
+        want = [h if h else "00" * 20 for h in r["hash160"]]
+        assert [g.hex() for g in got] == want, r["start"]
+
+
+@pytest.mark.parametrize("start", [1, 2**32 - 5, 2**64, N - 2**16 - 3, 0x2832ED74F2B5E35EE - 1000])
+def test_hash160_batch_vs_oracle(runner, start):
+    n = 1 << 16
+    got = b"".join(runner.generate_batch(start, n))
+    want = oracle.hash160_batch(start, n)
+    assert got == want
+
+
+def test_hash160_batch_edges(runner):
+    # scalar 0 and scalars >= n yield zeros (invalid keys, src/address.rs:93)
+    got = runner.generate_batch(0, 5000)
+    assert got[0] == b"\0" * 20
+    assert b"".join(got[1:]) == oracle.hash160_batch(1, 4999)
+    got = runner.generate_batch(N - 3000, 5000)
+    assert b"".join(got[:3000]) == oracle.hash160_batch(N - 3000, 3000)
+    assert all(g == b"\0" * 20 for g in got[3000:])
+    # ragged sizes
+    for n in (1, 2, 1023, 1025, 4097):
+        assert b"".join(runner.generate_batch(12345, n)) == oracle.hash160_batch(12345, n)
+    assert runner.generate_batch(1, 0) == []
+
+
+@pytest.mark.parametrize("fmt", FORMATS)
+def test_digest_batch_all_formats(small_runner, fmt):
+    rng = random.Random(42)
+    for start in (1, rng.randrange(1, N - 10**6)):
+        n = 20000
+        got = small_runner.digest_batch(fmt, start, n)
+        raw = oracle.digest_batch(fmt, start, n)
+        want = b"".join(raw[32 * i:32 * i + 20] for i in range(n))
+        assert got == want, (fmt, start)
+
+
+def test_multi_window_walk_consistency(small_runner):
+    # 3+ windows of the small runner: the next-centre update (C + W*G) is exercised
+    n = small_runner.batch_size * 3 + 777
+    start = 2**64 + 99
+    got = small_runner.digest_batch("p2pkh", start, n)
+    for off in (0, small_runner.batch_size - 5, 2 * small_runner.batch_size - 3, n - 2000):
+        m = 2000
+        assert got[20 * off:20 * (off + m)] == oracle.hash160_batch(start + off, m)
+    assert hashlib.sha256(got).hexdigest() == hashlib.sha256(b"".join(small_runner.generate_batch(start, n))).hexdigest()
+
+
+def _scan(runner, fmt, pat, start, n, ci=False, count=0):
+    cfg = vg.ScanConfig(format=vg.AddressFormat.parse(fmt), count=count, start=start, end=start + n - 1)
+    return vg.scan_gpu_with_runner(vg.Pattern(pat, ci), cfg, None, None, runner)
+
+
+def _check_scan(runner, fmt, pat, start, n, ci=False):
+    res = _scan(runner, fmt, pat, start, n, ci)
+    keys, ops, _ = oracle.scan_range(fmt, pat, start, n, ci=ci)
+    assert [int(m.hex, 16) for m in res.matches] == keys, (fmt, pat)
+    assert res.operations == ops
+    for m in res.matches:
+        a, w, _ = oracle.address(fmt, int(m.hex, 16))
+        assert (m.address, m.wif) == (a, w)
+    return res
+
+
+@pytest.mark.parametrize("fmt,pat,ci", [
+    ("p2pkh", "^1Ca", False), ("p2pkh", "^1cat", True), ("p2pkh", "^1[Cc]a", False), ("p2pkh", "^11", False),
+    ("p2pkh-uncompressed", "^1Ab", False), ("p2sh-p2wpkh", "^3Ab", False), ("p2sh-p2wpkh", "^3", False),
+    ("p2wpkh", "^bc1qaa", False), ("p2wpkh", "dead$", False), ("p2wpkh", "aa.*zz", False),
+    ("ethereum", "^0xdea", False), ("ethereum", "^0xDe", False), ("ethereum", "^0xab", True), ("ethereum", "F00$", False),
+    ("p2pkh", "abc$", False), ("p2pkh", "[0-9]{4}$", False), ("p2pkh", "^1.*XYZ", False), ("p2pkh", "^3", False),
+])
+def test_scan_match_sets_small(small_runner, fmt, pat, ci):
+    _check_scan(small_runner, fmt, pat, 2**64, 1 << 18, ci)
+
+
+def test_scan_edges(small_runner):
+    # range that includes scalar 0 (skipped, not counted) and dense pattern `.` (range's default, src/lib.rs:519)
+    res = _scan(small_runner, "p2pkh", ".", 0, 3000)
+    assert [int(m.hex, 16) for m in res.matches] == list(range(1, 3000)) and res.operations == 2999
+    # tail of the group: stops at n-1
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=0, start=N - 500, end=None)
+    res = vg.scan_gpu_with_runner(vg.Pattern("^1"), cfg, None, None, small_runner)
+    assert [int(m.hex, 16) for m in res.matches] == list(range(N - 500, N)) and res.operations == 500
+    # count: first `count` matches in ascending key order (src/gpu.rs:1095-1104)
+    res = _scan(small_runner, "p2pkh", "^1A", 1, 1 << 16, count=3)
+    keys, _, _ = oracle.scan_range("p2pkh", "^1A", 1, 1 << 16)
+    assert [int(m.hex, 16) for m in res.matches] == keys[:3]
+    # single key range, ragged end
+    res = _scan(small_runner, "p2pkh", ".", 77, 1)
+    assert [int(m.hex, 16) for m in res.matches] == [77]
+    # end < start is rejected cleanly (the reference underflows, src/scanner.rs:228)
+    with pytest.raises(Exception):
+        small_runner.scan_raw(10, 5)
+
+
+def test_scan_exact_address_planted(runner):
+    # C5 shape at reduced size: exact-address pattern for a planted key inside a multi-window range
+    start = 2**65
+    n = runner.batch_size * 2 + 12345
+    off = int(0.83 * n)
+    addr = oracle.address("p2pkh", start + off)[0]
+    res = _scan(runner, "p2pkh", "^" + addr + "$", start, n)
+    assert [int(m.hex, 16) for m in res.matches] == [start + off]
+    assert res.matches[0].address == addr and res.operations == n
+    assert runner.matcher_kind() == "exact"
+
+
+def test_config_c1_full_match_set(runner):
+    """BASELINE.json config C1: 2^24-key window from 2^64, P2PKH, ^1Cat — full match set vs the oracle."""
+    res = _check_scan(runner, "p2pkh", "^1Cat", 2**64, 1 << 24)
+    assert 150 < len(res.matches) < 300          # ~217 expected
+    assert all(m.address.startswith("1Cat") for m in res.matches)
+
+
+def test_sharded_scan_equals_single(runner):
+    """Two shard contexts (as two torchrun ranks would hold) cover the range disjointly: union == single-context set."""
+    start, n = 2**64, runner.batch_size * 4 + 999
+    single = _scan(runner, "p2pkh", "^1Ca", start, n)
+    parts = []
+    ops = 0
+    for i in range(2):
+        r = vg.GpuRunner(shard=(i, 2))
+        try:
+            res = _scan(r, "p2pkh", "^1Ca", start, n)
+            parts += [int(m.hex, 16) for m in res.matches]
+            ops += res.operations
+        finally:
+            r.close()
+    assert sorted(parts) == [int(m.hex, 16) for m in single.matches]
+    assert len(set(parts)) == len(parts) and ops == n
+
+
+def test_stop_flag_and_progress(small_runner):
+    stop = vg.StopFlag()
+    seen = []
+
+    def cb(k):
+        seen.append(k)
+        if len(seen) == 3:
+            stop.set()
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=0, start=2**64, end=2**64 + (1 << 30))
+    res = vg.scan_gpu_with_runner(vg.Pattern("^1CatDogs"), cfg, cb, stop, small_runner)
+    assert seen == sorted(seen) and len(seen) >= 3
+    assert res.operations < (1 << 30)

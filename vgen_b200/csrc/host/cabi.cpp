@@ -2,6 +2,7 @@
 #include "../../../include/vgen_cuda.h"
 #include "engine.h"
 #include <string.h>
+#include <stdio.h>
 #include <new>
 
 struct vgen_ctx {
@@ -116,6 +117,10 @@ int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t
     return VGEN_OK;
 }
 uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.launches : 0; }
+void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h) {
+    if (h2d) *h2d = ctx ? ctx->engine.h2d_bytes : 0;
+    if (d2h) *d2h = ctx ? ctx->engine.d2h_bytes : 0;
+}
 uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx) { return ctx ? ctx->engine.levels().back().window : 0; }
 
 int vgen_format_address(int format, const uint8_t *digest, char *out, size_t cap) {
@@ -142,6 +147,26 @@ int vgen_pattern_is_match(const char *pattern, int ci, const char *text) {
         if (!vg::compile_pattern(pattern, ci != 0, d, info, err)) return VGEN_ERR_PATTERN;
     } catch (const std::exception &) { return VGEN_ERR_PATTERN; }
     return d.match(text, strlen(text)) ? 1 : 0;
+}
+
+int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, size_t cap) {
+    if (!pattern || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;
+    vg::LoweredPattern lp; std::string err;
+    try {
+        if (!vg::lower_pattern(format, pattern, ci != 0, lp, err)) return VGEN_ERR_PATTERN;
+    } catch (const std::exception &) { return VGEN_ERR_PATTERN; }
+    std::string s = lp.kind_name;
+    char buf[64];
+    if (lp.dev.kind == VG_MATCH_INTERVALS)
+        for (int i = 0; i < lp.dev.n_intervals; i++) {
+            snprintf(buf, sizeof buf, ";%08x%08x-%08x%08x", lp.dev.lo_hi[i][0], lp.dev.lo_hi[i][1], lp.dev.lo_hi[i][2], lp.dev.lo_hi[i][3]);
+            s += buf;
+        }
+    if (lp.dev.kind == VG_MATCH_EXACT) {
+        s += ";exact=";
+        for (int i = 0; i < lp.dev.exact_words * 4; i++) { snprintf(buf, sizeof buf, "%02x", (lp.dev.exact[i / 4] >> (8 * (i % 4))) & 0xff); s += buf; }
+    }
+    return copy_out(s, out, cap);
 }
 
 }  // extern "C"

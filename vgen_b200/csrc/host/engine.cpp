@@ -159,7 +159,7 @@ bool Engine::setup_centers(Lane &L, int level, const U256 &window_base, std::str
     uint32_t k8[8]; first.to_limbs32(k8);
     CK(cudaMemcpyAsync(L.d_base8, k8, 32, cudaMemcpyHostToDevice, L.stream));
     CK(launch_points_of_scalars(L.d_centers, V.threads, L.d_base8, 2ull * half_, L.d_pow2, L.stream));
-    launches++;
+    launches++; h2d_bytes += 32;
     L.centers_level = level;
     return true;
 }
@@ -183,8 +183,9 @@ bool Engine::launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uin
     P.dump = dump; P.dump_stride = dump_stride;
     CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
     CK(launch_walk(fmt, mode, P, levels_[S.level].blocks, L.stream));
-    launches++;
+    launches++; h2d_bytes += sizeof(vg_scan_params);            // kernel parameters travel with the launch
     CK(cudaMemcpyAsync(S.h_counters, S.d_counters, kCounterWords * 4, cudaMemcpyDeviceToHost, L.stream));
+    d2h_bytes += kCounterWords * 4;
     CK(cudaEventRecord(S.done, L.stream));
     S.busy = true;
     return true;
@@ -283,6 +284,7 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
             uint32_t chunk = (uint32_t)std::min<size_t>(n_hits - done, L.h_hits_cap);
             CK(cudaMemcpyAsync(L.h_hits, S.d_hits + done, (size_t)chunk * sizeof(vg_hit_rec), cudaMemcpyDeviceToHost, L.copy_stream));
             CK(cudaStreamSynchronize(L.copy_stream));
+            d2h_bytes += (uint64_t)chunk * sizeof(vg_hit_rec);
             for (uint32_t i = 0; i < chunk; i++) {
                 const vg_hit_rec &R = L.h_hits[i];
                 Hit h; memset(h.digest, 0, 32);
@@ -323,6 +325,12 @@ bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *ou
     if (format < 0 || format > 5 || stride == 0 || stride > 32) { err = "invalid format or stride"; return false; }
     if (n == 0) return true;
     if (n > (1ull << 28)) { err = "digest_batch is limited to 2^28 keys per call"; return false; }
+    memset(out, 0, (size_t)n * stride);
+    if (!(start <= secp_order_minus1())) return true;           // every scalar invalid: all zeros
+    {   // scalars >= n are invalid (zeros): only walk up to n-1
+        U256 room = secp_order_minus1().sub(start).add64(1);
+        if (room.fits64() && room.w[0] < n) n = room.w[0];
+    }
     Lane &L = lanes_[0];
     CK(cudaSetDevice(L.device));
     uint32_t saved_idx = shard_index_, saved_cnt = shard_count_;

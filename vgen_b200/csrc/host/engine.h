@@ -66,6 +66,7 @@ public:
     uint32_t half() const { return half_; }
     const std::vector<Level> &levels() const { return levels_; }
     uint64_t launches = 0;        // kernel launches issued so far (walk + slow + set-up)
+    uint64_t h2d_bytes = 0, d2h_bytes = 0;   // bytes copied host->device / device->host by scans so far
 private:
     bool setup_centers(Lane &L, int level, const U256 &window_base, std::string &err);
     bool compute_stride_points(std::string &err);

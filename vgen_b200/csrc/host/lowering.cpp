@@ -197,6 +197,7 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
         if (!merged.empty() && (r.first <= merged.back().second || r.first == merged.back().second + 1)) merged.back().second = std::max(merged.back().second, r.second);
         else merged.push_back(r);
     }
+    if (merged.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; return true; }   // e.g. ^3 on P2PKH
     if (merged.size() > VG_MAX_INTERVALS) return true;   // too fragmented: keep the DFA path
     if (merged.size() == 1 && merged[0].first == 0 && merged[0].second == ~0ULL) {
         // the prefix constrains nothing (e.g. ^1 on P2PKH, ^bc1q on P2WPKH): only worth a prefilter if the rest does

@@ -1,0 +1,187 @@
+"""GpuRunner / scan_gpu_with_runner / scan_gpu — the reference's GPU scan surface (src/gpu.rs:18-63,128-136,138,
+535-665,920-1166) over libvgen_cuda.so. Same names and argument meaning; the wgpu backends are replaced by CUDA, and
+there is no CPU fallback: if the library or a B200 is missing, construction raises."""
+import ctypes as C
+import enum
+import secrets
+import time
+
+from . import _cabi
+from .address import AddressFormat, GeneratedAddress, address_from_digest, wif_from_key
+from .pattern import Pattern
+from .scanner import ScanConfig, ScanResult
+
+DEFAULT_BATCH_SIZE = 512 * 1024          # src/gpu.rs:83; here only a keys-per-launch hint (0 = fill the GPU)
+SECP256K1_N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
+
+
+class GpuBackend(enum.Enum):             # src/gpu.rs:18-26, plus Cuda; the graphics backends do not exist here
+    Auto = "auto"
+    Cuda = "CUDA"
+    Vulkan = "Vulkan"
+    Metal = "Metal"
+    Dx12 = "DX12"
+    Gl = "OpenGL"
+
+    def name_str(self):
+        return self.value
+
+    def __str__(self):
+        return self.value
+
+
+def _be(k):
+    return int(k).to_bytes(32, "big")
+
+
+class GpuRunner:
+    """GpuRunner::new(batch_size, backend) (src/gpu.rs:138). `devices` selects CUDA devices (default [0]);
+    `shard=(index, count)` lets one process per GPU split a range with disjoint start scalars and a common stride."""
+
+    def __init__(self, batch_size=0, backend=GpuBackend.Auto, devices=None, shard=None, stream=None):
+        if backend not in (GpuBackend.Auto, GpuBackend.Cuda):
+            raise RuntimeError("backend %s is not available: this build drives B200 GPUs through CUDA only" % backend)
+        L = _cabi.lib()
+        devs = list(devices) if devices else [0]
+        arr = (C.c_int * len(devs))(*devs)
+        ctx = C.c_void_p()
+        rc = L.vgen_cuda_create(arr, len(devs), int(batch_size or 0), C.byref(ctx))
+        if rc != 0:
+            raise _cabi.VgenError(rc, (L.vgen_cuda_last_error(None) or b"").decode())
+        self._ctx = ctx
+        self._lib = L
+        self.devices = devs
+        self.batch_size = int(L.vgen_cuda_window_keys(ctx))
+        name = C.create_string_buffer(256)
+        L.vgen_cuda_device_name(devs[0], name, 256)
+        self.device_name = name.value.decode()
+        self._backend = GpuBackend.Cuda
+        if shard is not None:
+            self._check(L.vgen_cuda_set_shard(ctx, int(shard[0]), int(shard[1])))
+        if stream is not None:
+            self._check(L.vgen_cuda_set_stream(ctx, 0, C.c_void_p(int(stream))))
+
+    @staticmethod
+    def new(batch_size=0, backend=GpuBackend.Auto, **kw):
+        return GpuRunner(batch_size, backend, **kw)
+
+    def backend(self):                                    # src/gpu.rs:134-136
+        return self._backend
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.vgen_cuda_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            raise _cabi.VgenError(rc, (self._lib.vgen_cuda_last_error(self._ctx) or b"").decode())
+
+    # -- reference-shaped batch API (generate_batch, src/gpu.rs:660-665): hash160 of n sequential keys
+    def generate_batch(self, start_key, n=None):
+        n = self.batch_size if n is None else int(n)
+        buf = C.create_string_buffer(20 * n)
+        self._check(self._lib.vgen_cuda_hash160_batch(self._ctx, _be(start_key), n, buf))
+        raw = buf.raw
+        return [raw[20 * i:20 * i + 20] for i in range(n)]
+
+    def digest_batch(self, fmt, start_key, n):
+        fmt = AddressFormat.parse(fmt)
+        stride = 32 if fmt == AddressFormat.P2tr else 20
+        buf = C.create_string_buffer(stride * n)
+        self._check(self._lib.vgen_cuda_digest_batch(self._ctx, int(fmt), _be(start_key), n, buf, stride))
+        return buf.raw
+
+    def set_pattern(self, pattern, fmt):
+        self._check(self._lib.vgen_cuda_set_pattern(self._ctx, int(AddressFormat.parse(fmt)), pattern.original().encode(),
+                                                    int(pattern.is_case_insensitive())))
+        return self._lib.vgen_cuda_matcher_kind(self._ctx).decode()
+
+    def matcher_kind(self):
+        return self._lib.vgen_cuda_matcher_kind(self._ctx).decode()
+
+    def launch_count(self):
+        return int(self._lib.vgen_cuda_launch_count(self._ctx))
+
+    def io_bytes(self):
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        self._lib.vgen_cuda_io_bytes(self._ctx, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def scan_raw(self, start, end, max_hits=0, stop=None, progress=None, hits_cap=1 << 20):
+        """vgen_cuda_scan: returns ([(key_int, digest_bytes, lane)], keys_scanned)."""
+        hits = (_cabi.VgenHit * hits_cap)()
+        n_hits = C.c_uint64(0)
+        scanned = C.c_uint64(0)
+        cb = _cabi.PROGRESS_FN(lambda k, u: progress(k)) if progress else C.cast(None, _cabi.PROGRESS_FN)
+        stop_p = C.cast(stop, C.POINTER(C.c_int32)) if stop is not None else None
+        rc = self._lib.vgen_cuda_scan(self._ctx, _be(start), None if end is None else _be(end), int(max_hits), stop_p, cb, None,
+                                      hits, hits_cap, C.byref(n_hits), C.byref(scanned))
+        self._check(rc)
+        out = [(int.from_bytes(bytes(h.key_be), "big"), bytes(h.digest)[:h.digest_len], h.device) for h in hits[:n_hits.value]]
+        return out, scanned.value
+
+    def bench_resident(self, start, n_windows):
+        ms = C.c_float(0)
+        keys = C.c_uint64(0)
+        launches = C.c_uint64(0)
+        self._check(self._lib.vgen_cuda_bench_resident(self._ctx, _be(start), n_windows, C.byref(ms), C.byref(keys), C.byref(launches)))
+        return ms.value, keys.value, launches.value
+
+
+class StopFlag:
+    """Arc<AtomicBool> of the reference (src/gpu.rs:924): a 32-bit flag the library polls after every window."""
+
+    def __init__(self):
+        self._v = C.c_int32(0)
+
+    def set(self):
+        self._v.value = 1
+
+    def is_set(self):
+        return self._v.value != 0
+
+    def _ptr(self):
+        return C.pointer(self._v)
+
+
+def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
+    """src/gpu.rs:920-1125: sequential scan from config.start (or a random valid key) to config.end, first `count`
+    matches in ascending key order. operations = exact valid keys tested (Appendix A of SURVEY.md)."""
+    if not isinstance(pattern, Pattern):
+        pattern = Pattern(pattern)
+    fmt = AddressFormat.parse(config.format)
+    if config.start is not None:
+        start = int(config.start)
+        if start == 0 and config.end is None:
+            raise ValueError("Invalid start key")                         # src/gpu.rs:903
+    else:
+        start = 1 + secrets.randbelow(SECP256K1_N - 1)                    # src/gpu.rs:933-945
+    end = None if config.end is None else int(config.end)
+    runner.set_pattern(pattern, fmt)
+    t0 = time.perf_counter()
+    count = int(config.count)
+    cap = min(count, 1 << 22) if count else 1 << 22
+    hits, scanned = runner.scan_raw(start, end, max_hits=count, stop=stop._ptr() if stop is not None else None,
+                                    progress=progress_cb, hits_cap=cap)
+    elapsed = time.perf_counter() - t0
+    matches = []
+    for key, digest, _lane in hits:
+        kb = _be(key)
+        matches.append(GeneratedAddress(address=address_from_digest(fmt, digest), wif=wif_from_key(fmt, kb), hex=kb.hex(), format=fmt))
+    return ScanResult(matches=matches, operations=scanned, elapsed_secs=elapsed)
+
+
+def scan_gpu(pattern, config, progress_cb=None, stop=None):
+    """src/gpu.rs:1127-1149: one-shot wrapper that builds its own runner."""
+    runner = GpuRunner(config.gpu_batch_size or 0, GpuBackend.Auto)
+    try:
+        return scan_gpu_with_runner(pattern, config, progress_cb, stop, runner)
+    finally:
+        runner.close()

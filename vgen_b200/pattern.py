@@ -1,0 +1,46 @@
+"""Pattern, mirroring src/pattern.rs:21-45 (Pattern::new / matches / original / is_case_insensitive). The regex engine
+is the library's own DFA compiler (Rust-`regex` syntax subset); the same DFA is what the device runs."""
+import ctypes as C
+
+from . import _cabi
+
+
+class Pattern:
+    def __init__(self, pattern, case_insensitive=False):
+        if pattern == "":
+            raise ValueError("Pattern cannot be empty")                      # src/pattern.rs:22-24
+        err = C.create_string_buffer(256)
+        rc = _cabi.lib().vgen_pattern_check(pattern.encode(), int(case_insensitive), err, 256)
+        if rc != 0:
+            raise ValueError("Invalid regex pattern: %s: %s" % (pattern, err.value.decode()))   # src/pattern.rs:32-33
+        self._pattern = pattern
+        self._ci = bool(case_insensitive)
+
+    @staticmethod
+    def new(pattern, case_insensitive=False):
+        return Pattern(pattern, case_insensitive)
+
+    def matches(self, address):                                              # src/pattern.rs:43-45
+        return _cabi.lib().vgen_pattern_is_match(self._pattern.encode(), int(self._ci), address.encode()) == 1
+
+    def original(self):
+        return self._pattern
+
+    def is_case_insensitive(self):
+        return self._ci
+
+    def lowering(self, fmt):
+        """How the scan path will test this pattern on the device for `fmt`: dict(kind=..., intervals=[(lo, hi), ...])."""
+        buf = C.create_string_buffer(4096)
+        rc = _cabi.lib().vgen_pattern_lowering(int(fmt), self._pattern.encode(), int(self._ci), buf, 4096)
+        if rc < 0:
+            raise _cabi.VgenError(rc, "vgen_pattern_lowering")
+        parts = buf.value.decode().split(";")
+        out = {"kind": parts[0], "intervals": [], "exact": None}
+        for p in parts[1:]:
+            if p.startswith("exact="):
+                out["exact"] = bytes.fromhex(p[6:])
+            elif p:
+                lo, hi = p.split("-")
+                out["intervals"].append((int(lo, 16), int(hi, 16)))
+        return out
