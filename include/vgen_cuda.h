@@ -102,6 +102,11 @@ int vgen_pattern_is_match(const char *pattern, int case_insensitive, const char 
 /* How (format, pattern) is lowered for the device, without touching a GPU. Writes
  * "<kind>[;<lo16hex>-<hi16hex>]*[;exact=<hex>]" (intervals over the leading 64 digest bits, inclusive);
  * returns the string length. kind as vgen_cuda_matcher_kind. */
+/* The dense DFA the device runs for (format, pattern): table[n_states*n_classes] (row-major next state), accept[n_states],
+ * sym_class[64] (encoder alphabet index -> class), info = {n_states, n_classes, start state after the fixed address head,
+ * flags}. Returns VGEN_ERR_BUFFER (info still filled) when a buffer is too small. For inspection and tests. */
+int vgen_pattern_dfa(int format, const char *pattern, int case_insensitive, uint16_t *table, size_t table_cap,
+                     uint8_t *accept, size_t accept_cap, uint8_t sym_class[64], uint32_t info[4]);
 int vgen_pattern_lowering(int format, const char *pattern, int case_insensitive, char *out, size_t cap);
 
 #ifdef __cplusplus

@@ -29,6 +29,17 @@ void emu_digest(int fmt, const uint32_t *x, const uint32_t *y, uint32_t *dg) {
         case 4: vg_digest_of_point<4>(dg, fx, fy); break; default: vg_digest_of_point<5>(dg, fx, fy); break;
     }
 }
+// on-device encoder + DFA of match.cuh for one digest: returns 1 when the device matcher accepts
+int emu_confirm(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_t *accept, const uint8_t *sym_class,
+                uint32_t n_classes, uint32_t start, uint32_t flags) {
+    vg_matcher_dev m; memset(&m, 0, sizeof m);
+    m.dfa.n_classes = n_classes; m.dfa.start = start; m.dfa.flags = flags;
+    vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
+    switch (fmt) {
+        case 0: return vg_confirm<0>(m, dv, dg); case 1: return vg_confirm<1>(m, dv, dg); case 2: return vg_confirm<2>(m, dv, dg);
+        case 3: return vg_confirm<3>(m, dv, dg); default: return vg_confirm<5>(m, dv, dg);
+    }
+}
 void emu_keccak_hex40(const uint32_t *m, uint32_t *out) { keccak_hex40(out, m); }
 
 // Walk n_windows windows of T threads x 2H keys from scalar `start`, dumping `stride` digest bytes per key.
@@ -54,15 +65,16 @@ int emu_walk_dump(int fmt, const uint32_t *start, uint32_t T, uint32_t H, uint32
     P.n_threads = T; P.half = H; P.centers = centers.data(); P.scratch = scratch.data(); P.gtab = gtab.data();
     P.limit = W; P.hit_count = &hitc; P.degen_count = &degc; P.degen_list = degl.data(); P.degen_cap = T;
     P.dump_stride = stride;
+    vg_dfa_view dv; dv.table = nullptr; dv.accept = nullptr; dv.sym = nullptr;
     for (uint32_t w = 0; w < n_windows; w++) {
         P.dump = out + (size_t)w * W * stride;
         for (uint32_t t = 0; t < T; t++) {
             switch (fmt) {
-                case 0: vg_walk_thread<0, VG_MODE_DUMP>(P, gtab.data(), t); break;
-                case 1: vg_walk_thread<1, VG_MODE_DUMP>(P, gtab.data(), t); break;
-                case 3: vg_walk_thread<3, VG_MODE_DUMP>(P, gtab.data(), t); break;
-                case 4: vg_walk_thread<4, VG_MODE_DUMP>(P, gtab.data(), t); break;
-                default: vg_walk_thread<5, VG_MODE_DUMP>(P, gtab.data(), t); break;
+                case 0: vg_walk_thread<0, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
+                case 1: vg_walk_thread<1, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
+                case 3: vg_walk_thread<3, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
+                case 4: vg_walk_thread<4, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
+                default: vg_walk_thread<5, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
             }
         }
     }

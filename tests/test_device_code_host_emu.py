@@ -102,3 +102,33 @@ def test_walk_vs_oracle(emu, fmt, start, T, H, nw):
         assert degen == 0 and not bad_batches
     else:
         assert degen > 0
+
+
+@pytest.mark.parametrize("fmt,pats", [
+    ("p2pkh", ["abc$", "^1Cat", "[0-9]{3}$", "^1.*Z", ".", "^11", "^1[a-z]+[A-Z]", "(?i)dog", "^1111", "x{2,}"]),
+    ("p2sh-p2wpkh", ["^3A", "aa$", "^3[0-9]", "(?i)cat"]),
+    ("p2wpkh", ["dead$", "^bc1qq", "^bc1q.*zz", "aaa", "^bc1q[02-9]+", "q$"]),
+    ("ethereum", ["^0xdead", "^0xDEAD", "(?i)^0xdead", "F00$", "^0x[0-9]{4}", "[A-F]{5}", "^0x00", "aB"]),
+    ("p2pkh-uncompressed", ["^1A", "zz$"]),
+])
+def test_device_matcher_vs_host_regex(emu, fmt, pats):
+    """match.cuh (on-device Base58Check / Bech32 / EIP-55 encoders feeding the DFA) must agree with the host's
+    regex over the address string (Pattern::matches, src/pattern.rs:43-45) on every digest."""
+    import vgen_b200 as vg
+    rng = random.Random(5)
+    F = vg.AddressFormat.parse(fmt)
+    digests = [bytes(rng.randrange(256) for _ in range(20)) for _ in range(400)]
+    digests += [b"\0" * 20, b"\0" * 19 + b"\1", b"\xff" * 20, b"\0\0\0" + bytes(rng.randrange(256) for _ in range(17)),
+                b"\0" + bytes(rng.randrange(256) for _ in range(19)), b"\0" * 10 + b"\xff" * 10]
+    emu.emu_confirm.argtypes = [C.c_int, C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32]
+    for pat in pats:
+        p = vg.Pattern(pat)
+        d = p.device_dfa(F)
+        n_hit = 0
+        for dg in digests:
+            words = (C.c_uint32 * 8)(*[int.from_bytes(dg[4 * i:4 * i + 4], "little") for i in range(5)], 0, 0, 0)
+            got = emu.emu_confirm(int(F), words, d["table"], d["accept"], d["sym_class"], d["n_classes"], d["start"], d["flags"])
+            addr = oracle.address_from_digest(fmt, dg)
+            want = oracle.regex_match(pat, addr)
+            assert bool(got) == want, (fmt, pat, addr)
+            n_hit += want

@@ -40,6 +40,7 @@ SYMBOLS = {
     "vgen_format_wif": (C.c_int, [C.c_int, C.c_char_p, C.c_char_p, C.c_size_t]),
     "vgen_pattern_check": (C.c_int, [C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]),
     "vgen_pattern_is_match": (C.c_int, [C.c_char_p, C.c_int, C.c_char_p]),
+    "vgen_pattern_dfa": (C.c_int, [C.c_int, C.c_char_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_uint32)]),
     "vgen_pattern_lowering": (C.c_int, [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]),
 }
 

@@ -149,6 +149,20 @@ int vgen_pattern_is_match(const char *pattern, int ci, const char *text) {
     return d.match(text, strlen(text)) ? 1 : 0;
 }
 
+int vgen_pattern_dfa(int format, const char *pattern, int ci, uint16_t *table, size_t table_cap, uint8_t *accept, size_t accept_cap,
+                     uint8_t sym_class[64], uint32_t info[4]) {
+    if (!pattern || !info || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;
+    vg::LoweredPattern lp; std::string err;
+    try {
+        if (!vg::lower_pattern(format, pattern, ci != 0, lp, err)) return VGEN_ERR_PATTERN;
+    } catch (const std::exception &) { return VGEN_ERR_PATTERN; }
+    info[0] = lp.dev.dfa.n_states; info[1] = lp.dev.dfa.n_classes; info[2] = lp.dev.dfa.start; info[3] = lp.dev.dfa.flags;
+    if (sym_class) memcpy(sym_class, lp.dev.dfa.sym_class, 64);
+    if (!table || !accept || table_cap < lp.dfa.table.size() || accept_cap < lp.dfa.accept_end.size()) return VGEN_ERR_BUFFER;
+    memcpy(table, lp.dfa.table.data(), lp.dfa.table.size() * 2);
+    memcpy(accept, lp.dfa.accept_end.data(), lp.dfa.accept_end.size());
+    return VGEN_OK;
+}
 int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, size_t cap) {
     if (!pattern || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;
     vg::LoweredPattern lp; std::string err;

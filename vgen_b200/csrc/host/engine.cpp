@@ -112,8 +112,8 @@ bool Engine::upload_dfa(std::string &err) {
         CK(cudaSetDevice(L.device));
         if (L.d_dfa_table) { cudaFree(L.d_dfa_table); L.d_dfa_table = nullptr; }
         if (L.d_dfa_accept) { cudaFree(L.d_dfa_accept); L.d_dfa_accept = nullptr; }
-        CK(cudaMalloc(&L.d_dfa_table, d.table.size() * 2));
-        CK(cudaMalloc(&L.d_dfa_accept, d.accept_end.size()));
+        CK(cudaMalloc(&L.d_dfa_table, d.table.size() * 2 + 4));     // the kernel stages these word-wise
+        CK(cudaMalloc(&L.d_dfa_accept, d.accept_end.size() + 4));
         CK(cudaMemcpy(L.d_dfa_table, d.table.data(), d.table.size() * 2, cudaMemcpyHostToDevice));
         CK(cudaMemcpy(L.d_dfa_accept, d.accept_end.data(), d.accept_end.size(), cudaMemcpyHostToDevice));
     }
@@ -124,8 +124,6 @@ bool Engine::set_pattern(int format, const std::string &pattern, bool ci, std::s
     LoweredPattern lp;
     if (!lower_pattern(format, pattern, ci, lp, err)) return false;
     lp_ = lp;
-    lp_.dev.dfa.n_states = lp_.dfa.n_states; lp_.dev.dfa.n_classes = lp_.dfa.n_classes; lp_.dev.dfa.start = lp_.dfa.start;
-    for (int c = 0; c < 128; c++) lp_.dev.dfa.class_of[c] = lp_.dfa.class_of[c];
     has_pattern_ = true;
     return upload_dfa(err);
 }
@@ -175,6 +173,7 @@ void Engine::fill_params(Lane &L, Slot &S, vg_scan_params &P) {
     P.degen_list = S.d_degen; P.degen_count = S.d_counters + 1; P.degen_cap = V.threads;
     P.m = lp_.dev;
     P.m.dfa.table = L.d_dfa_table; P.m.dfa.accept = L.d_dfa_accept;
+    P.dfa_smem_bytes = (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa) ? dfa_smem_bytes(P.m.dfa) : 0;
 }
 
 bool Engine::launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uint32_t dump_stride, std::string &err) {

@@ -149,7 +149,37 @@ bool decode_exact(int format, const std::string &addr, uint8_t digest[32]) {
         }
     }
 }
+// device view of the DFA for `format`: alphabet-index -> class map, start state advanced over the fixed head of the
+// address, and whether hex-letter case matters (Ethereum)
+void fill_device_dfa(int format, const Dfa &dfa, vg_dfa_dev &d) {
+    memset(&d, 0, sizeof d);
+    d.n_states = dfa.n_states; d.n_classes = dfa.n_classes; d.start = dfa.start;
+    auto adv = [&](const char *head) { for (const char *c = head; *c; c++) d.start = dfa.table[(size_t)d.start * dfa.n_classes + dfa.class_of[(uint8_t)*c]]; };
+    switch (format) {
+        case VG_FMT_P2PKH: case VG_FMT_P2PKH_UNCOMPRESSED: case VG_FMT_P2SH_P2WPKH:
+            for (int i = 0; i < 58; i++) d.sym_class[i] = dfa.class_of[(uint8_t)B58_ALPHABET[i]];
+            break;
+        case VG_FMT_P2WPKH: case VG_FMT_P2TR:
+            for (int i = 0; i < 32; i++) d.sym_class[i] = dfa.class_of[(uint8_t)BECH32_ALPHABET[i]];
+            adv(format == VG_FMT_P2WPKH ? "bc1q" : "bc1p");
+            break;
+        default:
+            for (int i = 0; i < 16; i++) {
+                d.sym_class[i] = dfa.class_of[(uint8_t)"0123456789abcdef"[i]];
+                d.sym_class[16 + i] = dfa.class_of[(uint8_t)"0123456789ABCDEF"[i]];
+                if (d.sym_class[i] != d.sym_class[16 + i]) d.flags |= 1u;
+            }
+            adv("0x");
+            break;
+    }
+}
 }  // namespace
+
+uint32_t dfa_smem_bytes(const vg_dfa_dev &d) {
+    uint64_t tw = ((uint64_t)d.n_states * d.n_classes + 1) / 2, aw = (d.n_states + 3) / 4;
+    uint64_t bytes = (tw + aw + 16) * 4;
+    return bytes <= 64 * 1024 ? (uint32_t)bytes : 0;
+}
 
 bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPattern &out, std::string &err) {
     out = LoweredPattern();
@@ -157,6 +187,7 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
     if (format < 0 || format > 5) { err = "invalid address format"; return false; }
     if (!compile_pattern(pattern, ci, out.dfa, out.info, err)) { err = "Invalid regex pattern: " + pattern + ": " + err; return false; }   // src/pattern.rs:32-33
     memset(&out.dev, 0, sizeof out.dev);
+    fill_device_dfa(format, out.dfa, out.dev.dfa);
     out.dev.kind = VG_MATCH_DFA;
     out.kind_name = "dfa";
     const PatternInfo &info = out.info;

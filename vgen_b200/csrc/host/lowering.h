@@ -15,5 +15,7 @@ struct LoweredPattern {
     vg_matcher_dev dev;      // device matcher (DFA table pointers are filled by the engine per device)
     std::string kind_name;   // "intervals" | "exact" | "dfa" | "all" | "none"
 };
+// shared-memory bytes the walk kernel needs to stage this DFA (table + accept + symbol classes), 0 if it is too large
+uint32_t dfa_smem_bytes(const vg_dfa_dev &d);
 bool lower_pattern(int format, const std::string &pattern, bool case_insensitive, LoweredPattern &out, std::string &err);
 }

@@ -79,10 +79,11 @@ __device__ __forceinline__ void vg_emit_hit(const vg_scan_params &P, bool is_hit
 }
 #endif
 
-template <int FMT> VG_DEV bool vg_confirm(const vg_matcher_dev &m, const uint32_t dg[VG_DIGEST_WORDS]);
+struct vg_dfa_view;
+template <int FMT> VG_DEV bool vg_confirm(const vg_matcher_dev &m, const vg_dfa_view &v, const uint32_t dg[VG_DIGEST_WORDS]);
 
 template <int FMT, int MODE>
-VG_DEV void vg_process_point(const vg_scan_params &P, fe &x, fe &y, unsigned long long idx, bool valid) {
+VG_DEV void vg_process_point(const vg_scan_params &P, const vg_dfa_view &dv, fe &x, fe &y, unsigned long long idx, bool valid) {
     fe_canon(x); fe_canon(y);
     uint32_t dg[VG_DIGEST_WORDS];
     vg_digest_of_point<FMT>(dg, x, y);
@@ -94,7 +95,7 @@ VG_DEV void vg_process_point(const vg_scan_params &P, fe &x, fe &y, unsigned lon
         }
     } else {
         bool hit = valid && vg_prefilter(P.m, dg);
-        if (hit && (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa)) hit = vg_confirm<FMT>(P.m, dg);
+        if (hit && (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa)) hit = vg_confirm<FMT>(P.m, dv, dg);
         vg_emit_hit(P, hit, idx, dg);
     }
 }
@@ -104,7 +105,7 @@ VG_DEV void vg_process_point(const vg_scan_params &P, fe &x, fe &y, unsigned lon
 
 // gtab: pointer to the i*G table (shared memory in the kernel), entry i-1 = 16 words
 template <int FMT, int MODE>
-VG_DEV void vg_walk_thread(const vg_scan_params &P, const uint32_t *gtab, uint32_t tid) {
+VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const uint32_t *gtab, uint32_t tid) {
     const uint32_t T = P.n_threads, H = P.half;
     fe cx, cy, sx, sy;
     VG_LOAD_FE(cx, P.centers + tid, T);
@@ -148,12 +149,12 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const uint32_t *gtab, uint32
             if (side) fe_neg(by, gy); else by = gy;
             affine_add_inv(x3, y3, cx, cy, gx, by, inv_i);
             unsigned long long idx = side ? idx_c - i : idx_c + i;
-            vg_process_point<FMT, MODE>(P, x3, y3, idx, !degenerate);
+            vg_process_point<FMT, MODE>(P, dv, x3, y3, idx, !degenerate);
         }
     }
     {   // the centre itself
         fe x3 = cx, y3 = cy;
-        vg_process_point<FMT, MODE>(P, x3, y3, idx_c, !degenerate);
+        vg_process_point<FMT, MODE>(P, dv, x3, y3, idx_c, !degenerate);
     }
     // next centre: C + W*G, with inv = 1/(Sx - Cx)
     fe nx, ny;
@@ -194,9 +195,9 @@ VG_DEV void vg_point_of_scalar(uint32_t *out, uint32_t n, uint32_t col, const ui
 }
 // slow generic path for one key: full scalar multiplication, every edge case handled
 template <int FMT, int MODE>
-VG_DEV void vg_slow_key(const vg_scan_params &P, const uint32_t k[8], unsigned long long idx, const uint32_t *pow2) {
+VG_DEV void vg_slow_key(const vg_scan_params &P, const vg_dfa_view &dv, const uint32_t k[8], unsigned long long idx, const uint32_t *pow2) {
     fe x, y;
     bool ok = scalar_is_valid(k) && scalar_mul_pow2(x, y, k, pow2);
     if (!ok) { fe_set_zero(x); fe_set_zero(y); }
-    vg_process_point<FMT, MODE>(P, x, y, idx, ok);
+    vg_process_point<FMT, MODE>(P, dv, x, y, idx, ok);
 }

@@ -16,8 +16,10 @@ struct vg_hit_rec {          // 40 bytes
 struct vg_dfa_dev {
     const uint16_t *table;   // [n_states][n_classes] next state
     const uint8_t *accept;   // [n_states] bit0: accepting if input ends here
-    uint32_t n_states, n_classes, start;
-    uint8_t class_of[128];   // ASCII -> class
+    uint32_t n_states, n_classes;
+    uint32_t start;          // start state, already advanced over the fixed head of the address ("bc1q", "0x")
+    uint32_t flags;          // bit 0: the DFA tells a-f from A-F (Ethereum: EIP-55 case must be computed on the device)
+    uint8_t sym_class[64];   // alphabet index of the format's encoder (base58 digit / bech32 value / hex nibble, +16 = upper case) -> class
 };
 struct vg_matcher_dev {
     int kind;
@@ -37,6 +39,7 @@ struct vg_scan_params {
     unsigned long long limit; // window keys with index < limit are inside the scan range
     vg_hit_rec *hits; uint32_t *hit_count; uint32_t hit_cap;
     uint32_t *degen_list; uint32_t *degen_count; uint32_t degen_cap;
+    uint32_t dfa_smem_bytes;  // shared-memory bytes for the DFA table + accept flags (0: read them from global memory)
     uint8_t *dump; uint32_t dump_stride;   // VG_MODE_DUMP: digest bytes per key index
     vg_matcher_dev m;
 };

@@ -44,3 +44,19 @@ class Pattern:
                 lo, hi = p.split("-")
                 out["intervals"].append((int(lo, 16), int(hi, 16)))
         return out
+
+    def device_dfa(self, fmt):
+        """The dense DFA the device runs for `fmt`: dict(table=bytes (uint16 LE), accept=bytes, sym_class=bytes, n_states, n_classes, start, flags)."""
+        L = _cabi.lib()
+        info = (C.c_uint32 * 4)()
+        sym = C.create_string_buffer(64)
+        rc = L.vgen_pattern_dfa(int(fmt), self._pattern.encode(), int(self._ci), None, 0, None, 0, sym, info)
+        if rc not in (0, -5):
+            raise _cabi.VgenError(rc, "vgen_pattern_dfa")
+        ns, nc = info[0], info[1]
+        table = C.create_string_buffer(2 * ns * nc)
+        accept = C.create_string_buffer(ns)
+        rc = L.vgen_pattern_dfa(int(fmt), self._pattern.encode(), int(self._ci), table, ns * nc, accept, ns, sym, info)
+        if rc != 0:
+            raise _cabi.VgenError(rc, "vgen_pattern_dfa")
+        return dict(table=table.raw, accept=accept.raw, sym_class=sym.raw, n_states=ns, n_classes=nc, start=info[2], flags=info[3])
