@@ -71,12 +71,18 @@ int vgen_cuda_set_shard(vgen_ctx *ctx, uint32_t shard_index, uint32_t shard_coun
 int vgen_cuda_set_stream(vgen_ctx *ctx, int lane, void *cuda_stream);
 
 /* Scan [start, end] inclusive (end == NULL: up to n-1) with the current pattern. Scalars 0 and >= n are
- * skipped and not counted (src/scanner.rs:294-295). Hits are written in ascending key order, at most
- * min(max_hits, hits_cap) of them (max_hits == 0: unlimited); *n_hits is the number written.
+ * skipped and not counted (src/scanner.rs:294-295). Hits are found in ascending key order, at most
+ * max_hits of them (0: unlimited); the first min(found, hits_cap) are written and *n_hits is that number (the rest
+ * stay readable through vgen_cuda_scan_fetch_hits).
  * `stop` (may be NULL) is polled after every window; progress (may be NULL) is called after every window. */
 int vgen_cuda_scan(vgen_ctx *ctx, const uint8_t start_be[32], const uint8_t *end_be, uint64_t max_hits,
                    const volatile int32_t *stop, vgen_progress_fn progress, void *user,
                    vgen_hit *hits_out, uint64_t hits_cap, uint64_t *n_hits, uint64_t *keys_scanned);
+
+/* The last scan keeps its full confirmed hit list (at most max_hits) inside the context: total count, and a reader for
+ * the hits that did not fit the caller's buffer (returns the number written). */
+uint64_t vgen_cuda_scan_total_hits(const vgen_ctx *ctx);
+uint64_t vgen_cuda_scan_fetch_hits(const vgen_ctx *ctx, uint64_t offset, vgen_hit *out, uint64_t cap);
 
 /* generate_batch (src/gpu.rs:660): hash160 of the compressed public key of n sequential scalars, 20 bytes
  * each; zeros for invalid scalars. */

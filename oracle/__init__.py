@@ -144,5 +144,6 @@ def scan_range(fmt, pattern, start, n_keys, ci=False, threads=None, cap=1 << 20)
         raise ValueError("invalid pattern: %r" % pattern)
     if found.value > cap:
         raise OverflowError("more matches than cap")
-    keys = sorted(int.from_bytes(out.raw[32 * i:32 * i + 32], "big") for i in range(found.value))
+    raw = out.raw[:32 * found.value]
+    keys = sorted(int.from_bytes(raw[32 * i:32 * i + 32], "big") for i in range(found.value))
     return keys, ops.value, el.value

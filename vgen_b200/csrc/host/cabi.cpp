@@ -8,7 +8,13 @@
 struct vgen_ctx {
     vg::Engine engine;
     std::string last_error;
+    std::vector<vg::Hit> hits;     // confirmed hits of the last scan, ascending by key
 };
+static void export_hit(const vg::Hit &h, vgen_hit &o) {
+    h.key.to_be(o.key_be);
+    memcpy(o.digest, h.digest, 32);
+    o.digest_len = h.digest_len; o.device = h.lane;
+}
 static thread_local std::string g_create_error;
 
 static int fail(vgen_ctx *ctx, int code, const std::string &msg) {
@@ -84,20 +90,23 @@ int vgen_cuda_scan(vgen_ctx *ctx, const uint8_t start_be[32], const uint8_t *end
     try {
         vg::U256 start = vg::U256::from_be(start_be), end;
         if (end_be) { end = vg::U256::from_be(end_be); if (end < start) return fail(ctx, VGEN_ERR_RANGE, "range end is below range start"); }
-        uint64_t want = max_hits ? std::min<uint64_t>(max_hits, hits_cap) : hits_cap;
-        std::vector<vg::Hit> hits;
+        std::vector<vg::Hit> &hits = ctx->hits;
+        hits.clear();
         vg::Engine::Progress cb;
         if (progress) cb = [&](uint64_t k) { progress(k, user); };
-        if (!ctx->engine.scan(start, end_be ? &end : nullptr, want, stop, cb, hits, *keys_scanned, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+        if (!ctx->engine.scan(start, end_be ? &end : nullptr, max_hits, stop, cb, hits, *keys_scanned, err)) return fail(ctx, VGEN_ERR_CUDA, err);
         uint64_t n = std::min<uint64_t>(hits.size(), hits_cap);
-        for (uint64_t i = 0; i < n; i++) {
-            hits[i].key.to_be(hits_out[i].key_be);
-            memcpy(hits_out[i].digest, hits[i].digest, 32);
-            hits_out[i].digest_len = hits[i].digest_len; hits_out[i].device = hits[i].lane;
-        }
+        for (uint64_t i = 0; i < n; i++) export_hit(hits[i], hits_out[i]);
         *n_hits = n;
     } catch (const std::exception &e) { return fail(ctx, VGEN_ERR_CUDA, e.what()); }
     return VGEN_OK;
+}
+uint64_t vgen_cuda_scan_total_hits(const vgen_ctx *ctx) { return ctx ? ctx->hits.size() : 0; }
+uint64_t vgen_cuda_scan_fetch_hits(const vgen_ctx *ctx, uint64_t offset, vgen_hit *out, uint64_t cap) {
+    if (!ctx || !out || offset >= ctx->hits.size()) return 0;
+    uint64_t n = std::min<uint64_t>(ctx->hits.size() - offset, cap);
+    for (uint64_t i = 0; i < n; i++) export_hit(ctx->hits[offset + i], out[i]);
+    return n;
 }
 int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride) {
     if (!ctx || !start_be || (!out && n)) return VGEN_ERR_INVALID_ARG;

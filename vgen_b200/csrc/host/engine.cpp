@@ -219,6 +219,20 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
     std::vector<U256> level_base(levels_.size());
     for (int lv = 1; lv <= fl; lv++) level_base[lv] = level_base[lv - 1].add(U256(levels_[lv - 1].window).mul64(G));
     std::vector<LaneRun> runs(nl);
+    // The small ramp windows exist so that a scan which can end early (a hit limit on a dense pattern, a short range) does
+    // not pay for a full window. When neither holds (no hit limit, or a sparse device matcher) start at the smallest level
+    // that covers the range in one round of windows, i.e. at full size for any long range.
+    int first_level = 0;
+    if (max_hits == 0 || lp_.dev.kind == VG_MATCH_INTERVALS || lp_.dev.kind == VG_MATCH_EXACT) {
+        first_level = fl;
+        for (int lv = 0; lv < fl; lv++) {
+            U256 cover = U256(levels_[lv].window).mul64(G);
+            if (!(cover < N)) { first_level = lv; break; }
+        }
+    }
+    for (int lv = 0; lv <= fl; lv++) level_base[lv] = U256(0);
+    for (int lv = first_level + 1; lv <= fl; lv++) level_base[lv] = level_base[lv - 1].add(U256(levels_[lv - 1].window).mul64(G));
+    for (auto &r : runs) r.level = first_level;
     uint64_t seq = 0;
     const int fmt = lp_.format;
 

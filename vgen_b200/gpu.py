@@ -114,17 +114,30 @@ class GpuRunner:
         self._lib.vgen_cuda_io_bytes(self._ctx, C.byref(a), C.byref(b))
         return a.value, b.value
 
-    def scan_raw(self, start, end, max_hits=0, stop=None, progress=None, hits_cap=1 << 20):
-        """vgen_cuda_scan: returns ([(key_int, digest_bytes, lane)], keys_scanned)."""
-        hits = (_cabi.VgenHit * hits_cap)()
+    def scan_raw(self, start, end, max_hits=0, stop=None, progress=None, hits_cap=4096):
+        """vgen_cuda_scan: returns ([(key_int, digest_bytes, lane)], keys_scanned). All hits are returned: those beyond the
+        first `hits_cap` are read back with vgen_cuda_scan_fetch_hits."""
+        if getattr(self, "_hitbuf_cap", 0) < hits_cap:
+            self._hitbuf = (_cabi.VgenHit * hits_cap)()
+            self._hitbuf_cap = hits_cap
+        hits = self._hitbuf
         n_hits = C.c_uint64(0)
         scanned = C.c_uint64(0)
         cb = _cabi.PROGRESS_FN(lambda k, u: progress(k)) if progress else C.cast(None, _cabi.PROGRESS_FN)
         stop_p = C.cast(stop, C.POINTER(C.c_int32)) if stop is not None else None
         rc = self._lib.vgen_cuda_scan(self._ctx, _be(start), None if end is None else _be(end), int(max_hits), stop_p, cb, None,
-                                      hits, hits_cap, C.byref(n_hits), C.byref(scanned))
+                                      hits, self._hitbuf_cap, C.byref(n_hits), C.byref(scanned))
         self._check(rc)
-        out = [(int.from_bytes(bytes(h.key_be), "big"), bytes(h.digest)[:h.digest_len], h.device) for h in hits[:n_hits.value]]
+
+        def conv(buf, n):
+            return [(int.from_bytes(bytes(h.key_be), "big"), bytes(h.digest)[:h.digest_len], h.device) for h in buf[:n]]
+        out = conv(hits, n_hits.value)
+        total = int(self._lib.vgen_cuda_scan_total_hits(self._ctx))
+        while len(out) < total:
+            n = int(self._lib.vgen_cuda_scan_fetch_hits(self._ctx, len(out), hits, self._hitbuf_cap))
+            if n == 0:
+                break
+            out += conv(hits, n)
         return out, scanned.value
 
     def bench_resident(self, start, n_windows):
@@ -167,9 +180,7 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
     runner.set_pattern(pattern, fmt)
     t0 = time.perf_counter()
     count = int(config.count)
-    cap = min(count, 1 << 22) if count else 1 << 22
-    hits, scanned = runner.scan_raw(start, end, max_hits=count, stop=stop._ptr() if stop is not None else None,
-                                    progress=progress_cb, hits_cap=cap)
+    hits, scanned = runner.scan_raw(start, end, max_hits=count, stop=stop._ptr() if stop is not None else None, progress=progress_cb)
     elapsed = time.perf_counter() - t0
     matches = []
     for key, digest, _lane in hits:
