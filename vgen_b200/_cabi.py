@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libvgen_cuda.so")
+# VGEN_CUDA_LIB: development override to load a differently-built library (kernel tuning variants)
+LIB_PATH = os.environ.get("VGEN_CUDA_LIB") or os.path.join(_HERE, "libvgen_cuda.so")
 
 VGEN_OK = 0
 ERR_NAMES = {-1: "invalid argument", -2: "CUDA error", -3: "invalid pattern", -4: "invalid range", -5: "buffer too small"}

@@ -16,13 +16,67 @@ static inline uint32_t vg_rotl(uint32_t x, int n) { return (x << n) | (x >> (32 
 static inline uint32_t vg_bswap(uint32_t x) { return __builtin_bswap32(x); }
 static inline uint32_t vg_shf_l(uint32_t lo, uint32_t hi, int n) { return (hi << n) | (lo >> (32 - n)); }  // 0<n<32
 #define VG_CONST static const
+// pipe-steering primitives (device: forced onto the multiplier pipe; host emulation: plain arithmetic)
+static inline uint32_t vg_addf(uint32_t a, uint32_t b) { return a + b; }
+static inline uint32_t vg_rotl_f(uint32_t x, int n) { return vg_rotl(x, n); }
+static inline uint32_t vg_shr_f(uint32_t x, int n) { return x >> n; }
 #else
 __device__ __forceinline__ uint32_t vg_rotr(uint32_t x, int n) { return __funnelshift_r(x, x, n); }
 __device__ __forceinline__ uint32_t vg_rotl(uint32_t x, int n) { return __funnelshift_l(x, x, n); }
 __device__ __forceinline__ uint32_t vg_bswap(uint32_t x) { return __byte_perm(x, 0, 0x0123); }
 __device__ __forceinline__ uint32_t vg_shf_l(uint32_t lo, uint32_t hi, int n) { return __funnelshift_l(lo, hi, n); }
 #define VG_CONST __device__ __constant__ const
+// ---- pipe steering -------------------------------------------------------------------------------------------
+// On sm_100 the add/logic/shift instructions (IADD3, LOP3, SHF, LEA) issue on the 64-lane ALU pipe and IMAD /
+// IMAD.WIDE on the 64-lane multiplier pipe. SHA-256 + RIPEMD-160 are ~95 % ALU-class work, so the ALU pipe binds
+// (ncu r01_a: ALU 74 % busy, multiplier pipe 32 %). These helpers move selected adds, rotations and shifts onto the
+// multiplier pipe. The multiplier 1 is read from constant memory so ptxas cannot fold the multiply back into an add.
+__device__ __constant__ uint32_t vg_one = 1;
+// a + b as IMAD (a * 1 + b). Callers use plain + where an operand pair is a compile-time constant.
+__device__ __forceinline__ uint32_t vg_addf(uint32_t a, uint32_t b) {
+    uint32_t r;
+    asm("mad.lo.u32 %0,%1,%2,%3;" : "=r"(r) : "r"(a), "r"(vg_one), "r"(b));
+    return r;
+}
+// rotl(x, n) = lo + hi of the 64-bit product x * 2^n (IMAD.WIDE + IMAD): two multiplier-pipe ops, no ALU op
+__device__ __forceinline__ uint32_t vg_rotl_f(uint32_t x, int n) {
+    uint32_t lo, hi, r;
+    asm("{ .reg .u64 p; mul.wide.u32 p,%2,%3; mov.b64 {%0,%1},p; }" : "=r"(lo), "=r"(hi) : "r"(x), "r"(1u << n));
+    asm("mad.lo.u32 %0,%1,%2,%3;" : "=r"(r) : "r"(lo), "r"(vg_one), "r"(hi));
+    return r;
+}
+// x >> n as the high half of x * 2^(32-n)
+__device__ __forceinline__ uint32_t vg_shr_f(uint32_t x, int n) {
+    uint32_t r;
+    asm("mul.hi.u32 %0,%1,%2;" : "=r"(r) : "r"(x), "r"(1u << (32 - n)));
+    return r;
+}
 #endif
+
+// ---- N independent hash instances advanced in lock-step ------------------------------------------------------------
+// The hashes below are written over a word type T: uint32_t, or vw<N> = N independent 32-bit lanes held by ONE thread.
+// The scan kernel hashes the +i and -i neighbours of a centre as vw<2>: two independent dependency chains in the same
+// instruction stream, which is what fills the issue slots a single SHA-256/RIPEMD-160 chain leaves empty (ncu r01_a:
+// 49 % issue utilisation, top stall = fixed-latency dependency wait).
+template <int N> struct vw { uint32_t v[N]; };
+#define VW_BIN(OP) \
+    template <int N> VG_DEV vw<N> operator OP(const vw<N> &a, const vw<N> &b) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = a.v[i] OP b.v[i]; return r; } \
+    template <int N> VG_DEV vw<N> operator OP(const vw<N> &a, uint32_t b) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = a.v[i] OP b; return r; } \
+    template <int N> VG_DEV vw<N> operator OP(uint32_t a, const vw<N> &b) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = a OP b.v[i]; return r; }
+VW_BIN(+) VW_BIN(^) VW_BIN(&) VW_BIN(|)
+#undef VW_BIN
+template <int N> VG_DEV vw<N> operator~(const vw<N> &a) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = ~a.v[i]; return r; }
+template <int N> VG_DEV vw<N> operator<<(const vw<N> &a, int n) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = a.v[i] << n; return r; }
+template <int N> VG_DEV vw<N> operator>>(const vw<N> &a, int n) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = a.v[i] >> n; return r; }
+#define VW_UN(F) template <int N> VG_DEV vw<N> F(const vw<N> &a, int n) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = F(a.v[i], n); return r; }
+VW_UN(vg_rotr) VW_UN(vg_rotl) VW_UN(vg_rotl_f) VW_UN(vg_shr_f)
+#undef VW_UN
+template <int N> VG_DEV vw<N> vg_bswap(const vw<N> &a) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = vg_bswap(a.v[i]); return r; }
+template <int N> VG_DEV vw<N> vg_shf_l(const vw<N> &lo, const vw<N> &hi, int n) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = vg_shf_l(lo.v[i], hi.v[i], n); return r; }
+template <int N> VG_DEV vw<N> vg_addf(const vw<N> &a, const vw<N> &b) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = vg_addf(a.v[i], b.v[i]); return r; }
+template <int N> VG_DEV vw<N> vg_addf(const vw<N> &a, uint32_t b) { vw<N> r; VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = vg_addf(a.v[i], b); return r; }
+VG_DEV void vg_splat(uint32_t &r, uint32_t c) { r = c; }
+template <int N> VG_DEV void vg_splat(vw<N> &r, uint32_t c) { VG_UNROLL for (int i = 0; i < N; i++) r.v[i] = c; }
 
 VG_CONST uint32_t VG_SHA_K[64] = {
     0x428a2f98,0x71374491,0xb5c0fbcf,0xe9b5dba5,0x3956c25b,0x59f111f1,0x923f82a4,0xab1c5ed5,
@@ -35,62 +89,80 @@ VG_CONST uint32_t VG_SHA_K[64] = {
     0x748f82ee,0x78a5636f,0x84c87814,0x8cc70208,0x90befffa,0xa4506ceb,0xbef9a3f7,0xc67178f2};
 
 #define VG_SHA_IV {0x6a09e667u,0xbb67ae85u,0x3c6ef372u,0xa54ff53au,0x510e527fu,0x9b05688cu,0x1f83d9abu,0x5be0cd19u}
+template <class T> VG_DEV void sha256_iv(T st[8]) {
+    const uint32_t iv[8] = VG_SHA_IV;
+    VG_UNROLL for (int i = 0; i < 8; i++) vg_splat(st[i], iv[i]);
+}
 
-// one compression; w[] is consumed as the rolling schedule
-VG_DEV void sha256_compress(uint32_t st[8], uint32_t w[16]) {
-    uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+// How many of the six rotations per SHA-256 round go to the multiplier pipe (0..2); tuned on the B200, see DESIGN.md
+#ifndef VG_SHA_ROT_FMA
+#define VG_SHA_ROT_FMA 0
+#endif
+// one compression; w[] is consumed as the rolling schedule.
+// Pipe split per round: S1, ch, S0, maj, t = p + S1 + ch, a = t + S0 + maj on the ALU pipe (12 ops);
+// K + w, p = h + (K + w), e = d + t on the multiplier pipe (3 ops). Schedule: 2 x (2 rotations + LOP3) + one 3-input add
+// on the ALU pipe, the two plain shifts and w[i-16] + w[i-7] on the multiplier pipe.
+// CMASK: bit i set = message word i is a compile-time constant (padding), so K + w folds and must not be forced
+// through an IMAD.
+template <uint32_t CMASK, class T>
+VG_DEV void sha256_compress(T st[8], T w[16]) {
+    T a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
     VG_UNROLL for (int i = 0; i < 64; i++) {
         if (i >= 16) {
-            uint32_t w15 = w[(i - 15) & 15], w2 = w[(i - 2) & 15];
-            uint32_t s0 = vg_rotr(w15, 7) ^ vg_rotr(w15, 18) ^ (w15 >> 3);
-            uint32_t s1 = vg_rotr(w2, 17) ^ vg_rotr(w2, 19) ^ (w2 >> 10);
-            w[i & 15] = w[i & 15] + s0 + w[(i - 7) & 15] + s1;
+            T w15 = w[(i - 15) & 15], w2 = w[(i - 2) & 15];
+            T s0 = vg_rotr(w15, 7) ^ vg_rotr(w15, 18) ^ vg_shr_f(w15, 3);
+            T s1 = vg_rotr(w2, 17) ^ vg_rotr(w2, 19) ^ vg_shr_f(w2, 10);
+            w[i & 15] = vg_addf(w[i & 15], w[(i - 7) & 15]) + s0 + s1;
         }
-        uint32_t S1 = vg_rotr(e, 6) ^ vg_rotr(e, 11) ^ vg_rotr(e, 25);
-        uint32_t ch = (e & f) ^ (~e & g);
-        uint32_t t1 = h + S1 + ch + VG_SHA_K[i] + w[i & 15];
-        uint32_t S0 = vg_rotr(a, 2) ^ vg_rotr(a, 13) ^ vg_rotr(a, 22);
-        uint32_t mj = (a & b) | (c & (a | b));
-        h = g; g = f; f = e; e = d + t1; d = c; c = b; b = a; a = t1 + S0 + mj;
+        T S1 = vg_rotr(e, 6) ^ vg_rotr(e, 11) ^ (VG_SHA_ROT_FMA >= 1 ? vg_rotl_f(e, 7) : vg_rotr(e, 25));
+        T ch = (e & f) ^ (~e & g);
+        T kw = (i < 16 && ((CMASK >> i) & 1u)) ? w[i & 15] + VG_SHA_K[i] : vg_addf(w[i & 15], VG_SHA_K[i]);
+        T p = vg_addf(h, kw);
+        T t1 = p + S1 + ch;
+        T S0 = vg_rotr(a, 2) ^ vg_rotr(a, 13) ^ (VG_SHA_ROT_FMA >= 2 ? vg_rotl_f(a, 10) : vg_rotr(a, 22));
+        T mj = (a & b) | (c & (a | b));
+        h = g; g = f; f = e; e = vg_addf(d, t1); d = c; c = b; b = a; a = t1 + S0 + mj;
     }
-    st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+    st[0] = vg_addf(st[0], a); st[1] = vg_addf(st[1], b); st[2] = vg_addf(st[2], c); st[3] = vg_addf(st[3], d);
+    st[4] = vg_addf(st[4], e); st[5] = vg_addf(st[5], f); st[6] = vg_addf(st[6], g); st[7] = vg_addf(st[7], h);
 }
-// SHA-256(prefix || X) for a 33-byte compressed key; x is a canonical field element
-VG_DEV void sha256_pub33(uint32_t out[8], uint32_t prefix, const fe &x) {
-    uint32_t w[16];
-    w[0] = (prefix << 24) | (x.v[7] >> 8);
-    VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(x.v[7 - k], x.v[8 - k], 24);
-    w[8] = (x.v[0] << 24) | 0x00800000u;
-    VG_UNROLL for (int k = 9; k < 15; k++) w[k] = 0;
-    w[15] = 33 * 8;
-    uint32_t st[8] = VG_SHA_IV;
-    sha256_compress(st, w);
-    VG_UNROLL for (int i = 0; i < 8; i++) out[i] = st[i];
+// SHA-256(prefix || X) for a 33-byte compressed key; xv = the 8 little-endian limbs of a canonical field element
+template <class T>
+VG_DEV void sha256_pub33(T out[8], const T &prefix, const T xv[8]) {
+    T w[16];
+    w[0] = (prefix << 24) | (xv[7] >> 8);
+    VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(xv[7 - k], xv[8 - k], 24);
+    w[8] = (xv[0] << 24) | 0x00800000u;
+    VG_UNROLL for (int k = 9; k < 15; k++) vg_splat(w[k], 0u);
+    vg_splat(w[15], 33 * 8);
+    sha256_iv(out);
+    sha256_compress<0xFE00u>(out, w);
 }
 // SHA-256(04 || X || Y) for a 65-byte uncompressed key (two blocks)
-VG_DEV void sha256_pub65(uint32_t out[8], const fe &x, const fe &y) {
-    uint32_t w[16];
-    w[0] = (4u << 24) | (x.v[7] >> 8);
-    VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(x.v[7 - k], x.v[8 - k], 24);
-    w[8] = (x.v[0] << 24) | (y.v[7] >> 8);
-    VG_UNROLL for (int k = 1; k < 8; k++) w[8 + k] = vg_shf_l(y.v[7 - k], y.v[8 - k], 24);
-    uint32_t st[8] = VG_SHA_IV;
-    sha256_compress(st, w);
-    w[0] = (y.v[0] << 24) | 0x00800000u;
-    VG_UNROLL for (int k = 1; k < 15; k++) w[k] = 0;
-    w[15] = 65 * 8;
-    sha256_compress(st, w);
-    VG_UNROLL for (int i = 0; i < 8; i++) out[i] = st[i];
+template <class T>
+VG_DEV void sha256_pub65(T out[8], const T xv[8], const T yv[8]) {
+    T w[16];
+    w[0] = (xv[7] >> 8) | (4u << 24);
+    VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(xv[7 - k], xv[8 - k], 24);
+    w[8] = (xv[0] << 24) | (yv[7] >> 8);
+    VG_UNROLL for (int k = 1; k < 8; k++) w[8 + k] = vg_shf_l(yv[7 - k], yv[8 - k], 24);
+    sha256_iv(out);
+    sha256_compress<0u>(out, w);
+    w[0] = (yv[0] << 24) | 0x00800000u;
+    VG_UNROLL for (int k = 1; k < 15; k++) vg_splat(w[k], 0u);
+    vg_splat(w[15], 65 * 8);
+    sha256_compress<0xFFFEu>(out, w);
 }
-// SHA-256 of a message of nbytes (<= 55) given as big-endian words (unused tail bytes must be 0)
-VG_DEV void sha256_short(uint32_t out[8], const uint32_t *m, int nbytes) {
-    uint32_t w[16];
-    VG_UNROLL for (int k = 0; k < 15; k++) w[k] = (k * 4 < nbytes + 1) ? m[k] : 0u;
-    w[nbytes >> 2] |= 0x80u << (24 - 8 * (nbytes & 3));
-    w[15] = (uint32_t)nbytes * 8;
-    uint32_t st[8] = VG_SHA_IV;
-    sha256_compress(st, w);
-    VG_UNROLL for (int i = 0; i < 8; i++) out[i] = st[i];
+// SHA-256 of a message of NBYTES (<= 55) given as big-endian words (unused tail bytes must be 0)
+template <int NBYTES, class T>
+VG_DEV void sha256_short(T out[8], const T *m) {
+    const int nbytes = NBYTES;
+    T w[16];
+    VG_UNROLL for (int k = 0; k < 15; k++) { if (k * 4 < nbytes + 1) w[k] = m[k]; else vg_splat(w[k], 0u); }
+    w[nbytes >> 2] = w[nbytes >> 2] | (0x80u << (24 - 8 * (nbytes & 3)));
+    vg_splat(w[15], (uint32_t)nbytes * 8);
+    sha256_iv(out);
+    sha256_compress<(0xFFFFu << (NBYTES / 4 + 1)) & 0xFFFFu>(out, w);
 }
 
 // ---- RIPEMD-160 of a 32-byte message given as 8 big-endian SHA words ----
@@ -99,16 +171,22 @@ VG_DEV void sha256_short(uint32_t out[8], const uint32_t *m, int nbytes) {
 #define VG_RMD_F2(x, y, z) (((x) | ~(y)) ^ (z))
 #define VG_RMD_F3(x, y, z) (((x) & (z)) | ((y) & ~(z)))
 #define VG_RMD_F4(x, y, z) ((x) ^ ((y) | ~(z)))
-#define VG_RMD_STEP(F, a, b, c, d, e, xw, k, s) \
-    a = vg_rotl(a + F(b, c, d) + (xw) + (k), s) + e; c = vg_rotl(c, 10);
+// ALU pipe: F (one LOP3), a + F + (x + k) (one IADD3), rotate-and-add e (one LEA.HI); multiplier pipe: x + k, rotl(c, 10)
+#define VG_RMD_STEP(F, a, b, c, d, e, xw, s) \
+    a = vg_rotl(a + F(b, c, d) + (xw), s) + e; c = vg_rotl_f(c, 10);
 
-VG_DEV void ripemd160_32(uint32_t out[5], const uint32_t sha[8]) {
-    uint32_t x[16];
+template <class T>
+VG_DEV void ripemd160_32(T out[5], const T sha[8]) {
+    T x[16];
     VG_UNROLL for (int i = 0; i < 8; i++) x[i] = vg_bswap(sha[i]);
-    x[8] = 0x80u; x[9] = 0; x[10] = 0; x[11] = 0; x[12] = 0; x[13] = 0; x[14] = 256u; x[15] = 0;
+    const uint32_t pad[8] = {0x80u, 0, 0, 0, 0, 0, 256u, 0};
+    VG_UNROLL for (int i = 0; i < 8; i++) vg_splat(x[8 + i], pad[i]);
     const uint32_t h0 = 0x67452301u, h1 = 0xEFCDAB89u, h2 = 0x98BADCFEu, h3 = 0x10325476u, h4 = 0xC3D2E1F0u;
-    uint32_t a = h0, b = h1, c = h2, d = h3, e = h4, A = h0, B = h1, C = h2, D = h3, E = h4;
-#define L(F, a, b, c, d, e, r, s, k) VG_RMD_STEP(F, a, b, c, d, e, x[r], k, s)
+    T a, b, c, d, e, A, B, C, D, E;
+    vg_splat(a, h0); vg_splat(b, h1); vg_splat(c, h2); vg_splat(d, h3); vg_splat(e, h4);
+    A = a; B = b; C = c; D = d; E = e;
+// x[8..15] are padding constants: x + k folds at compile time there
+#define L(F, a, b, c, d, e, r, s, k) VG_RMD_STEP(F, a, b, c, d, e, ((r) >= 8 || (k) == 0u ? x[r] + (k) : vg_addf(x[r], k)), s)
     // left line
     L(VG_RMD_F0,a,b,c,d,e,0,11,0u) L(VG_RMD_F0,e,a,b,c,d,1,14,0u) L(VG_RMD_F0,d,e,a,b,c,2,15,0u) L(VG_RMD_F0,c,d,e,a,b,3,12,0u)
     L(VG_RMD_F0,b,c,d,e,a,4,5,0u) L(VG_RMD_F0,a,b,c,d,e,5,8,0u) L(VG_RMD_F0,e,a,b,c,d,6,7,0u) L(VG_RMD_F0,d,e,a,b,c,7,9,0u)
@@ -160,25 +238,27 @@ VG_DEV void ripemd160_32(uint32_t out[5], const uint32_t sha[8]) {
     L(VG_RMD_F0,D,E,A,B,C,6,8,0u) L(VG_RMD_F0,C,D,E,A,B,2,13,0u) L(VG_RMD_F0,B,C,D,E,A,13,6,0u) L(VG_RMD_F0,A,B,C,D,E,14,5,0u)
     L(VG_RMD_F0,E,A,B,C,D,0,15,0u) L(VG_RMD_F0,D,E,A,B,C,3,13,0u) L(VG_RMD_F0,C,D,E,A,B,9,11,0u) L(VG_RMD_F0,B,C,D,E,A,11,11,0u)
 #undef L
-    out[0] = h1 + c + D; out[1] = h2 + d + E; out[2] = h3 + e + A; out[3] = h4 + a + B; out[4] = h0 + b + C;
+    out[0] = c + D + h1; out[1] = d + E + h2; out[2] = e + A + h3; out[3] = a + B + h4; out[4] = b + C + h0;
 }
 // hash160 words (little-endian: digest byte 4i+j = byte j of out[i])
-VG_DEV void hash160_pub33(uint32_t out[5], uint32_t prefix, const fe &x) {
-    uint32_t s[8]; sha256_pub33(s, prefix, x); ripemd160_32(out, s);
+template <class T>
+VG_DEV void hash160_pub33(T out[5], const T &prefix, const T xv[8]) {
+    T s[8]; sha256_pub33(s, prefix, xv); ripemd160_32(out, s);
 }
-VG_DEV void hash160_pub65(uint32_t out[5], const fe &x, const fe &y) {
-    uint32_t s[8]; sha256_pub65(s, x, y); ripemd160_32(out, s);
+template <class T>
+VG_DEV void hash160_pub65(T out[5], const T xv[8], const T yv[8]) {
+    T s[8]; sha256_pub65(s, xv, yv); ripemd160_32(out, s);
 }
 // hash160(00 14 || h) : the P2SH-P2WPKH redeem-script hash (src/address.rs:130-135)
-VG_DEV void hash160_p2sh_script(uint32_t out[5], const uint32_t h[5]) {
-    uint32_t B[5], m[6], s[8];
+template <class T>
+VG_DEV void hash160_p2sh_script(T out[5], const T h[5]) {
+    T B[5], mm[15], s[8];
     VG_UNROLL for (int i = 0; i < 5; i++) B[i] = vg_bswap(h[i]);
-    m[0] = 0x00140000u | (B[0] >> 16);
-    VG_UNROLL for (int i = 1; i < 5; i++) m[i] = (B[i - 1] << 16) | (B[i] >> 16);
-    m[5] = B[4] << 16;
-    uint32_t mm[15];
-    VG_UNROLL for (int i = 0; i < 15; i++) mm[i] = i < 6 ? m[i] : 0u;
-    sha256_short(s, mm, 22);
+    mm[0] = (B[0] >> 16) | 0x00140000u;
+    VG_UNROLL for (int i = 1; i < 5; i++) mm[i] = (B[i - 1] << 16) | (B[i] >> 16);
+    mm[5] = B[4] << 16;
+    VG_UNROLL for (int i = 6; i < 15; i++) vg_splat(mm[i], 0u);
+    sha256_short<22>(s, mm);
     ripemd160_32(out, s);
 }
 

@@ -58,11 +58,7 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
         min_sm = std::min(min_sm, L.sm_count);
         lanes_.push_back(L);
     }
-    uint32_t full_blocks = (uint32_t)min_sm * 2;       // __launch_bounds__(256, 2): two resident CTAs per SM
-    if (hint) full_blocks = std::max<uint32_t>(1, std::min<uint32_t>(hint / (VG_BLOCK * 2 * half_), 8u * min_sm));
-    levels_.clear();
-    for (uint32_t b : {1u, 8u, 64u}) if (b * 4 <= full_blocks) levels_.push_back({b, b * VG_BLOCK, (uint64_t)b * VG_BLOCK * 2 * half_});
-    levels_.push_back({full_blocks, full_blocks * VG_BLOCK, (uint64_t)full_blocks * VG_BLOCK * 2 * half_});
+    levels_ = compute_levels(min_sm, hint, half_, VG_BLOCK);
     const Level &F = levels_.back();
     for (auto &L : lanes_) {
         CK(cudaSetDevice(L.device));
@@ -191,7 +187,7 @@ bool Engine::launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uin
 }
 
 namespace {
-struct LaneRun { int level = 0; uint64_t k = 0; bool done = false; U256 expect_base; bool have_expect = false; };
+struct LaneRun { LaneCursor cur; bool done = false; U256 expect_base; bool have_expect = false; };
 }
 
 bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, const volatile int32_t *stop, const Progress &progress,
@@ -216,54 +212,33 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
     if (!compute_stride_points(err)) return false;
     const uint32_t nl = (uint32_t)lanes_.size(), G = shard_count_ * nl;
     const int fl = (int)levels_.size() - 1;
-    std::vector<U256> level_base(levels_.size());
-    for (int lv = 1; lv <= fl; lv++) level_base[lv] = level_base[lv - 1].add(U256(levels_[lv - 1].window).mul64(G));
+    // ramp levels only when the scan can end early: a hit limit on a matcher that may be dense (plan.h)
+    const bool sparse = lp_.dev.kind == VG_MATCH_INTERVALS || lp_.dev.kind == VG_MATCH_EXACT;
+    const WindowPlan plan(levels_, G, N, max_hits != 0 && !sparse);
     std::vector<LaneRun> runs(nl);
-    // The small ramp windows exist so that a scan which can end early (a hit limit on a dense pattern, a short range) does
-    // not pay for a full window. When neither holds (no hit limit, or a sparse device matcher) start at the smallest level
-    // that covers the range in one round of windows, i.e. at full size for any long range.
-    int first_level = 0;
-    if (max_hits == 0 || lp_.dev.kind == VG_MATCH_INTERVALS || lp_.dev.kind == VG_MATCH_EXACT) {
-        first_level = fl;
-        for (int lv = 0; lv < fl; lv++) {
-            U256 cover = U256(levels_[lv].window).mul64(G);
-            if (!(cover < N)) { first_level = lv; break; }
-        }
-    }
-    for (int lv = 0; lv <= fl; lv++) level_base[lv] = U256(0);
-    for (int lv = first_level + 1; lv <= fl; lv++) level_base[lv] = level_base[lv - 1].add(U256(levels_[lv - 1].window).mul64(G));
-    for (auto &r : runs) r.level = first_level;
+    for (auto &r : runs) r.cur = plan.begin();
     uint64_t seq = 0;
     const int fmt = lp_.format;
 
-    auto next_offset = [&](uint32_t li) -> U256 {
-        const LaneRun &r = runs[li];
-        uint64_t gl = (uint64_t)shard_index_ * nl + li;
-        U256 idx = r.level < fl ? U256(gl) : U256(r.k).mul64(G).add64(gl);
-        // idx * window (idx < 2^64 * 2^32 safely inside 256 bits)
-        U256 off = idx.mul64(levels_[r.level].window);
-        return level_base[r.level].add(off);
-    };
     std::deque<std::pair<uint32_t, int>> inflight;
     auto issue = [&](uint32_t li) -> bool {
         Lane &L = lanes_[li]; LaneRun &r = runs[li];
         if (r.done) return true;
         int s = !L.slot[0].busy ? 0 : (!L.slot[1].busy ? 1 : -1);
         if (s < 0) return true;
-        U256 off = next_offset(li);
-        if (!(off < N)) { r.done = true; return true; }
+        U256 off; uint64_t limit;
+        if (!plan.window(shard_index_ * nl + li, r.cur, off, limit)) { r.done = true; return true; }
         if (cudaSetDevice(L.device) != cudaSuccess) { err = "cudaSetDevice failed"; return false; }
         Slot &S = L.slot[s];
-        S.base = start.add(off); S.level = r.level; S.seq = seq++;
-        U256 remain = N.sub(off);
-        S.limit = (remain.fits64() && remain.w[0] < levels_[r.level].window) ? remain.w[0] : levels_[r.level].window;
-        if (L.centers_level != r.level || !r.have_expect || !(r.expect_base == S.base)) {
-            if (!setup_centers(L, r.level, S.base, err)) return false;
+        const int level = r.cur.level;
+        S.base = start.add(off); S.level = level; S.seq = seq++; S.limit = limit;
+        if (L.centers_level != level || !r.have_expect || !(r.expect_base == S.base)) {
+            if (!setup_centers(L, level, S.base, err)) return false;
         }
         if (!launch_window(L, s, fmt, VG_MODE_MATCH, nullptr, 0, err)) return false;
         // after this launch the centres stand at base + G*W of the same level
-        r.expect_base = S.base.add(U256(levels_[r.level].window).mul64(G)); r.have_expect = true;
-        if (r.level < fl) { r.level++; r.have_expect = false; } else r.k++;
+        r.expect_base = S.base.add(plan.stride(level)); r.have_expect = level == fl;
+        plan.advance(r.cur);
         inflight.push_back({li, s});
         return true;
     };

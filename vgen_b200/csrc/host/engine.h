@@ -7,13 +7,12 @@
 #include <vector>
 #include <functional>
 #include "lowering.h"
+#include "plan.h"
 #include "../kernels.h"
 
 namespace vg {
 
 struct Hit { U256 key; uint8_t digest[32]; uint32_t digest_len; uint32_t lane; };
-
-struct Level { uint32_t blocks; uint32_t threads; uint64_t window; };   // ramp level geometry
 
 struct Slot {                 // one of the two windows a lane keeps in flight
     vg_hit_rec *d_hits = nullptr;

@@ -34,8 +34,9 @@ VG_DEV uint32_t sha256_32_first_word(const uint32_t in[8]) {
     w[8] = 0x80000000u;
     VG_UNROLL for (int i = 9; i < 15; i++) w[i] = 0;
     w[15] = 256;
-    uint32_t st[8] = VG_SHA_IV;
-    sha256_compress(st, w);
+    uint32_t st[8];
+    sha256_iv(st);
+    sha256_compress<0xFF00u>(st, w);
     return st[0];
 }
 
@@ -51,7 +52,7 @@ VG_DEV bool vg_match_base58check(const vg_matcher_dev &m, const vg_dfa_view &v, 
     msg[5] = B[4] << 24;
     VG_UNROLL for (int i = 6; i < 15; i++) msg[i] = 0;
     uint32_t h1[8];
-    sha256_short(h1, msg, 21);
+    sha256_short<21>(h1, msg);
     uint32_t ck = sha256_32_first_word(h1);
     // 25-byte payload as a 200-bit big-endian number in 7 limbs, n[6] = top 8 bits = version
     uint32_t n[7];

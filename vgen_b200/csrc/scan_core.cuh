@@ -14,27 +14,37 @@
 #include "hash.cuh"
 #include "scan_types.h"
 
-template <int FMT>
-VG_DEV void vg_digest_of_point(uint32_t dg[VG_DIGEST_WORDS], const fe &x, const fe &y) {
-    VG_UNROLL for (int i = 5; i < VG_DIGEST_WORDS; i++) dg[i] = 0;
+// digest words of N points at once (T = uint32_t or vw<N>); xv / yv = little-endian limbs of canonical coordinates
+template <int FMT, class T>
+VG_DEV void vg_digest_lanes(T dg[VG_DIGEST_WORDS], const T xv[8], const T yv[8]) {
+    VG_UNROLL for (int i = 5; i < VG_DIGEST_WORDS; i++) vg_splat(dg[i], 0u);
     if (FMT == VG_FMT_P2PKH || FMT == VG_FMT_P2WPKH) {
-        hash160_pub33(dg, 2u + (y.v[0] & 1u), x);
+        hash160_pub33(dg, (yv[0] & 1u) + 2u, xv);
     } else if (FMT == VG_FMT_P2PKH_UNCOMPRESSED) {
-        hash160_pub65(dg, x, y);
+        hash160_pub65(dg, xv, yv);
     } else if (FMT == VG_FMT_P2SH_P2WPKH) {
-        uint32_t h[5]; hash160_pub33(h, 2u + (y.v[0] & 1u), x); hash160_p2sh_script(dg, h);
-    } else if (FMT == VG_FMT_ETHEREUM) {
-        keccak_eth_address(dg, x, y);
+        T h[5]; hash160_pub33(h, (yv[0] & 1u) + 2u, xv); hash160_p2sh_script(dg, h);
     } else {   // P2TR fast path yields the even-Y internal key x (as src/shaders/search_p2tr.wgsl:104-113)
-        VG_UNROLL for (int i = 0; i < 8; i++) dg[i] = vg_bswap(x.v[7 - i]);
+        VG_UNROLL for (int i = 0; i < 8; i++) dg[i] = vg_bswap(xv[7 - i]);
     }
 }
+template <int FMT>
+VG_DEV void vg_digest_of_point(uint32_t dg[VG_DIGEST_WORDS], const fe &x, const fe &y) {
+    if (FMT == VG_FMT_ETHEREUM) {
+        VG_UNROLL for (int i = 5; i < VG_DIGEST_WORDS; i++) dg[i] = 0;
+        keccak_eth_address(dg, x, y);
+    } else {
+        vg_digest_lanes<FMT, uint32_t>(dg, x.v, y.v);
+    }
+}
+// lanes hashed together by one thread: 2 for the hash160 formats (the +i / -i pair), 1 for Keccak (register budget)
+template <int FMT> struct vg_ilp { static const int N = (FMT == VG_FMT_ETHEREUM) ? 1 : 2; };
 
 VG_DEV bool vg_prefilter(const vg_matcher_dev &m, const uint32_t dg[VG_DIGEST_WORDS]) {
     if (m.kind == VG_MATCH_ALL || m.kind == VG_MATCH_DFA) return true;
     if (m.kind == VG_MATCH_EXACT) {
         uint32_t d = 0;
-        for (int i = 0; i < m.exact_words; i++) d |= dg[i] ^ m.exact[i];
+        VG_UNROLL for (int i = 0; i < VG_DIGEST_WORDS; i++) d |= (i < m.exact_words) ? (dg[i] ^ m.exact[i]) : 0u;   // static indices: dg stays in registers
         return d == 0;
     }
     uint32_t hi = vg_bswap(dg[0]), lo = vg_bswap(dg[1]);
@@ -82,21 +92,48 @@ __device__ __forceinline__ void vg_emit_hit(const vg_scan_params &P, bool is_hit
 struct vg_dfa_view;
 template <int FMT> VG_DEV bool vg_confirm(const vg_matcher_dev &m, const vg_dfa_view &v, const uint32_t dg[VG_DIGEST_WORDS]);
 
+// test / dump one already-computed digest
 template <int FMT, int MODE>
-VG_DEV void vg_process_point(const vg_scan_params &P, const vg_dfa_view &dv, fe &x, fe &y, unsigned long long idx, bool valid) {
-    fe_canon(x); fe_canon(y);
-    uint32_t dg[VG_DIGEST_WORDS];
-    vg_digest_of_point<FMT>(dg, x, y);
+VG_DEV void vg_finish_point(const vg_scan_params &P, const vg_dfa_view &dv, const uint32_t dg[VG_DIGEST_WORDS], unsigned long long idx, bool valid) {
     valid = valid && idx < P.limit;
     if (MODE == VG_MODE_DUMP) {
         if (valid) {
             uint8_t *o = P.dump + idx * P.dump_stride;
-            for (uint32_t b = 0; b < P.dump_stride; b++) o[b] = (uint8_t)(dg[b >> 2] >> (8 * (b & 3)));
+            for (uint32_t b = 0; b < P.dump_stride; b++) {
+                uint32_t wsel = 0;
+                VG_UNROLL for (int i = 0; i < VG_DIGEST_WORDS; i++) wsel = ((b >> 2) == (uint32_t)i) ? dg[i] : wsel;
+                o[b] = (uint8_t)(wsel >> (8 * (b & 3)));
+            }
         }
     } else {
         bool hit = valid && vg_prefilter(P.m, dg);
         if (hit && (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa)) hit = vg_confirm<FMT>(P.m, dv, dg);
         vg_emit_hit(P, hit, idx, dg);
+    }
+}
+template <int FMT, int MODE>
+VG_DEV void vg_process_point(const vg_scan_params &P, const vg_dfa_view &dv, fe &x, fe &y, unsigned long long idx, bool valid) {
+    fe_canon(x); fe_canon(y);
+    uint32_t dg[VG_DIGEST_WORDS];
+    vg_digest_of_point<FMT>(dg, x, y);
+    vg_finish_point<FMT, MODE>(P, dv, dg, idx, valid);
+}
+// the +/- pair of one walk step: both digests are computed in lock-step (vw<2>) where the format allows
+template <int FMT, int MODE>
+VG_DEV void vg_process_pair(const vg_scan_params &P, const vg_dfa_view &dv, fe &x0, fe &y0, unsigned long long idx0,
+                            fe &x1, fe &y1, unsigned long long idx1, bool valid) {
+    if (vg_ilp<FMT>::N == 2) {
+        fe_canon(x0); fe_canon(y0); fe_canon(x1); fe_canon(y1);
+        vw<2> xv[8], yv[8], dg[VG_DIGEST_WORDS];
+        VG_UNROLL for (int l = 0; l < 8; l++) { xv[l].v[0] = x0.v[l]; xv[l].v[1] = x1.v[l]; yv[l].v[0] = y0.v[l]; yv[l].v[1] = y1.v[l]; }
+        vg_digest_lanes<FMT, vw<2> >(dg, xv, yv);
+        uint32_t d0[VG_DIGEST_WORDS], d1[VG_DIGEST_WORDS];
+        VG_UNROLL for (int i = 0; i < VG_DIGEST_WORDS; i++) { d0[i] = dg[i].v[0]; d1[i] = dg[i].v[1]; }
+        vg_finish_point<FMT, MODE>(P, dv, d0, idx0, valid);
+        vg_finish_point<FMT, MODE>(P, dv, d1, idx1, valid);
+    } else {
+        vg_process_point<FMT, MODE>(P, dv, x0, y0, idx0, valid);
+        vg_process_point<FMT, MODE>(P, dv, x1, y1, idx1, valid);
     }
 }
 
@@ -141,20 +178,15 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const
         fe_sub(dx, gx, cx);
         if (fe_is_zero_raw(dx)) fe_set_one(dx);
         fe_mul(inv, inv, dx);
-#ifndef VG_HOST_EMU
-        #pragma unroll 1
-#endif
-        for (int side = (i == H ? 1 : 0); side < 2; side++) {
-            fe x3, y3, by;
-            if (side) fe_neg(by, gy); else by = gy;
-            affine_add_inv(x3, y3, cx, cy, gx, by, inv_i);
-            unsigned long long idx = side ? idx_c - i : idx_c + i;
-            vg_process_point<FMT, MODE>(P, dv, x3, y3, idx, !degenerate);
-        }
-    }
-    {   // the centre itself
-        fe x3 = cx, y3 = cy;
-        vg_process_point<FMT, MODE>(P, dv, x3, y3, idx_c, !degenerate);
+        // +i and -i share inv_i (x(iG) = x(-iG)). At i == H the + side belongs to the next thread's batch: the centre
+        // itself takes its place so that every step hashes exactly two keys.
+        fe xp, yp, xm, ym, ngy;
+        fe_neg(ngy, gy);
+        affine_add_inv(xm, ym, cx, cy, gx, ngy, inv_i);
+        unsigned long long idx_p = idx_c + i;
+        if (i == H) { xp = cx; yp = cy; idx_p = idx_c; }
+        else affine_add_inv(xp, yp, cx, cy, gx, gy, inv_i);
+        vg_process_pair<FMT, MODE>(P, dv, xp, yp, idx_p, xm, ym, idx_c - i, !degenerate);
     }
     // next centre: C + W*G, with inv = 1/(Sx - Cx)
     fe nx, ny;
