@@ -84,6 +84,11 @@ int vgen_cuda_scan(vgen_ctx *ctx, const uint8_t start_be[32], const uint8_t *end
 uint64_t vgen_cuda_scan_total_hits(const vgen_ctx *ctx);
 uint64_t vgen_cuda_scan_fetch_hits(const vgen_ctx *ctx, uint64_t offset, vgen_hit *out, uint64_t cap);
 
+/* Bulk form of what scan_gpu_with_runner builds per match (src/gpu.rs:1062-1090: address string, WIF, key): for hits
+ * [offset, offset+cap) of the last scan writes 32-byte big-endian keys and NUL-terminated address / WIF strings at
+ * `stride` (>= 96) bytes per hit. Any of the three outputs may be NULL. Returns the number of hits written. */
+uint64_t vgen_cuda_scan_fetch_records(const vgen_ctx *ctx, uint64_t offset, uint64_t cap, uint8_t *keys32, char *addresses, char *wifs, size_t stride);
+
 /* generate_batch (src/gpu.rs:660): hash160 of the compressed public key of n sequential scalars, 20 bytes
  * each; zeros for invalid scalars. */
 int vgen_cuda_hash160_batch(vgen_ctx *ctx, const uint8_t start_be[32], uint64_t n, uint8_t *out20);
@@ -108,6 +113,14 @@ int vgen_pattern_is_match(const char *pattern, int case_insensitive, const char 
 /* How (format, pattern) is lowered for the device, without touching a GPU. Writes
  * "<kind>[;<lo16hex>-<hi16hex>]*[;exact=<hex>]" (intervals over the leading 64 digest bits, inclusive);
  * returns the string length. kind as vgen_cuda_matcher_kind. */
+/* The window schedule of a scan, without touching a GPU (host arithmetic only; what vgen_cuda_scan follows): the windows
+ * that global lane `lane` of `global_lanes` (= shard_count x GPUs per context) takes from [start, end] on devices with
+ * `sm_count` SMs. Writes up to cap windows (first key, big-endian, 32 bytes each; keys inside the range) and returns the
+ * total number of windows of that lane. can_end_early != 0 selects the ramped schedule used for hit-limited dense scans.
+ * Lanes own disjoint windows whose union is exactly the valid part of the range. */
+int64_t vgen_plan_windows(const uint8_t start_be[32], const uint8_t end_be[32], int sm_count, uint32_t keys_per_launch_hint,
+                          uint32_t global_lanes, uint32_t lane, int can_end_early, uint8_t *first_keys_be, uint64_t *n_keys, uint64_t cap);
+
 /* The dense DFA the device runs for (format, pattern): table[n_states*n_classes] (row-major next state), accept[n_states],
  * sym_class[64] (encoder alphabet index -> class), info = {n_states, n_classes, start state after the fixed address head,
  * flags}. Returns VGEN_ERR_BUFFER (info still filled) when a buffer is too small. For inspection and tests. */

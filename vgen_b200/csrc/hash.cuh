@@ -31,15 +31,29 @@ __device__ __forceinline__ uint32_t vg_shf_l(uint32_t lo, uint32_t hi, int n) { 
 // IMAD.WIDE on the 64-lane multiplier pipe. SHA-256 + RIPEMD-160 are ~95 % ALU-class work, so the ALU pipe binds
 // (ncu r01_a: ALU 74 % busy, multiplier pipe 32 %). These helpers move selected adds, rotations and shifts onto the
 // multiplier pipe. The multiplier 1 is read from constant memory so ptxas cannot fold the multiply back into an add.
+// MEASURED (B200, r01, tools/variants.sh): every steering variant is SLOWER than leaving pipe selection to ptxas
+// (5.12-5.37 vs 5.82 Gkeys/s): peak_bench shows the two pipes do not add up on this chip (pure ALU 19.3, pure IMAD 16.8,
+// 1:1 mix only 25.6 T inst/s), so trading one ALU op for 1-2 IMADs loses. All three switches therefore default to 0.
+#ifndef VG_STEER_ADD
+#define VG_STEER_ADD 0
+#endif
+#ifndef VG_STEER_ROT
+#define VG_STEER_ROT 0
+#endif
+#ifndef VG_STEER_SHR
+#define VG_STEER_SHR 0
+#endif
 __device__ __constant__ uint32_t vg_one = 1;
 // a + b as IMAD (a * 1 + b). Callers use plain + where an operand pair is a compile-time constant.
 __device__ __forceinline__ uint32_t vg_addf(uint32_t a, uint32_t b) {
+    if (!VG_STEER_ADD) return a + b;
     uint32_t r;
     asm("mad.lo.u32 %0,%1,%2,%3;" : "=r"(r) : "r"(a), "r"(vg_one), "r"(b));
     return r;
 }
 // rotl(x, n) = lo + hi of the 64-bit product x * 2^n (IMAD.WIDE + IMAD): two multiplier-pipe ops, no ALU op
 __device__ __forceinline__ uint32_t vg_rotl_f(uint32_t x, int n) {
+    if (!VG_STEER_ROT) return __funnelshift_l(x, x, n);
     uint32_t lo, hi, r;
     asm("{ .reg .u64 p; mul.wide.u32 p,%2,%3; mov.b64 {%0,%1},p; }" : "=r"(lo), "=r"(hi) : "r"(x), "r"(1u << n));
     asm("mad.lo.u32 %0,%1,%2,%3;" : "=r"(r) : "r"(lo), "r"(vg_one), "r"(hi));
@@ -47,6 +61,7 @@ __device__ __forceinline__ uint32_t vg_rotl_f(uint32_t x, int n) {
 }
 // x >> n as the high half of x * 2^(32-n)
 __device__ __forceinline__ uint32_t vg_shr_f(uint32_t x, int n) {
+    if (!VG_STEER_SHR) return x >> n;
     uint32_t r;
     asm("mul.hi.u32 %0,%1,%2;" : "=r"(r) : "r"(x), "r"(1u << (32 - n)));
     return r;

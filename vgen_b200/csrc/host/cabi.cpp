@@ -108,6 +108,19 @@ uint64_t vgen_cuda_scan_fetch_hits(const vgen_ctx *ctx, uint64_t offset, vgen_hi
     for (uint64_t i = 0; i < n; i++) export_hit(ctx->hits[offset + i], out[i]);
     return n;
 }
+uint64_t vgen_cuda_scan_fetch_records(const vgen_ctx *ctx, uint64_t offset, uint64_t cap, uint8_t *keys32, char *addresses, char *wifs, size_t stride) {
+    if (!ctx || offset >= ctx->hits.size() || stride < 96) return 0;
+    const int fmt = ctx->engine.pattern().format;
+    uint64_t n = std::min<uint64_t>(ctx->hits.size() - offset, cap);
+    for (uint64_t i = 0; i < n; i++) {
+        const vg::Hit &h = ctx->hits[offset + i];
+        uint8_t kb[32]; h.key.to_be(kb);
+        if (keys32) memcpy(keys32 + 32 * i, kb, 32);
+        if (addresses) { std::string a = vg::format_address(fmt, h.digest); strncpy(addresses + stride * i, a.c_str(), stride - 1); addresses[stride * i + stride - 1] = 0; }
+        if (wifs) { std::string w = vg::format_wif(fmt, kb); strncpy(wifs + stride * i, w.c_str(), stride - 1); wifs[stride * i + stride - 1] = 0; }
+    }
+    return n;
+}
 int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride) {
     if (!ctx || !start_be || (!out && n)) return VGEN_ERR_INVALID_ARG;
     std::string err;
@@ -158,6 +171,31 @@ int vgen_pattern_is_match(const char *pattern, int ci, const char *text) {
     return d.match(text, strlen(text)) ? 1 : 0;
 }
 
+int64_t vgen_plan_windows(const uint8_t start_be[32], const uint8_t end_be[32], int sm_count, uint32_t keys_per_launch_hint,
+                          uint32_t global_lanes, uint32_t lane, int can_end_early, uint8_t *first_keys_be, uint64_t *n_keys, uint64_t cap) {
+    if (!start_be || !end_be || sm_count <= 0 || global_lanes == 0 || lane >= global_lanes) return VGEN_ERR_INVALID_ARG;
+    vg::U256 start = vg::U256::from_be(start_be), end = vg::U256::from_be(end_be);
+    if (end < start) return VGEN_ERR_RANGE;
+    if (start.is_zero()) start = vg::U256(1);
+    if (vg::secp_order_minus1() < end) end = vg::secp_order_minus1();
+    if (end < start) return 0;
+    const vg::U256 N = end.sub(start).add64(1);
+    std::vector<vg::Level> levels = vg::compute_levels(sm_count, keys_per_launch_hint, 512, VG_BLOCK, VG_CTAS_PER_SM);
+    vg::WindowPlan plan(levels, global_lanes, N, can_end_early != 0);
+    vg::LaneCursor c = plan.begin();
+    int64_t n = 0;
+    vg::U256 off; uint64_t limit;
+    while (plan.window(lane, c, off, limit)) {
+        if ((uint64_t)n < cap) {
+            if (first_keys_be) start.add(off).to_be(first_keys_be + 32 * n);
+            if (n_keys) n_keys[n] = limit;
+        }
+        n++;
+        plan.advance(c);
+        if (n > (1 << 24)) break;
+    }
+    return n;
+}
 int vgen_pattern_dfa(int format, const char *pattern, int ci, uint16_t *table, size_t table_cap, uint8_t *accept, size_t accept_cap,
                      uint8_t sym_class[64], uint32_t info[4]) {
     if (!pattern || !info || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;

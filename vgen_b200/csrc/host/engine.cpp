@@ -58,7 +58,7 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
         min_sm = std::min(min_sm, L.sm_count);
         lanes_.push_back(L);
     }
-    levels_ = compute_levels(min_sm, hint, half_, VG_BLOCK);
+    levels_ = compute_levels(min_sm, hint, half_, VG_BLOCK, VG_CTAS_PER_SM);
     const Level &F = levels_.back();
     for (auto &L : lanes_) {
         CK(cudaSetDevice(L.device));

@@ -13,8 +13,8 @@ namespace vg {
 struct Level { uint32_t blocks; uint32_t threads; uint64_t window; };   // launch geometry of one ramp level
 
 // levels for a device with `sm_count` SMs: optional small ramp levels, then the full-size level
-inline std::vector<Level> compute_levels(int sm_count, uint32_t keys_per_launch_hint, uint32_t half, uint32_t block) {
-    uint32_t full_blocks = (uint32_t)sm_count * 2;       // two resident CTAs per SM
+inline std::vector<Level> compute_levels(int sm_count, uint32_t keys_per_launch_hint, uint32_t half, uint32_t block, uint32_t ctas_per_sm) {
+    uint32_t full_blocks = (uint32_t)sm_count * ctas_per_sm;       // one full wave of resident CTAs
     if (keys_per_launch_hint) {
         uint32_t b = keys_per_launch_hint / (block * 2 * half);
         full_blocks = b < 1 ? 1 : (b > 8u * sm_count ? 8u * sm_count : b);

@@ -3,7 +3,13 @@
 #include <cuda_runtime.h>
 #include "scan_types.h"
 
+#ifndef VG_BLOCK
 #define VG_BLOCK 256
+#endif
+// resident CTAs per SM the walk kernel is compiled for (__launch_bounds__) and the full-size window is sized for
+#ifndef VG_CTAS_PER_SM
+#define VG_CTAS_PER_SM 2
+#endif
 
 namespace vg {
 cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, cudaStream_t s);

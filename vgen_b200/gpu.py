@@ -114,7 +114,7 @@ class GpuRunner:
         self._lib.vgen_cuda_io_bytes(self._ctx, C.byref(a), C.byref(b))
         return a.value, b.value
 
-    def scan_raw(self, start, end, max_hits=0, stop=None, progress=None, hits_cap=4096):
+    def scan_raw(self, start, end, max_hits=0, stop=None, progress=None, hits_cap=4096, fetch_all=True):
         """vgen_cuda_scan: returns ([(key_int, digest_bytes, lane)], keys_scanned). All hits are returned: those beyond the
         first `hits_cap` are read back with vgen_cuda_scan_fetch_hits."""
         if getattr(self, "_hitbuf_cap", 0) < hits_cap:
@@ -132,7 +132,7 @@ class GpuRunner:
         def conv(buf, n):
             return [(int.from_bytes(bytes(h.key_be), "big"), bytes(h.digest)[:h.digest_len], h.device) for h in buf[:n]]
         out = conv(hits, n_hits.value)
-        total = int(self._lib.vgen_cuda_scan_total_hits(self._ctx))
+        total = int(self._lib.vgen_cuda_scan_total_hits(self._ctx)) if fetch_all else 0
         while len(out) < total:
             n = int(self._lib.vgen_cuda_scan_fetch_hits(self._ctx, len(out), hits, self._hitbuf_cap))
             if n == 0:
@@ -140,12 +140,43 @@ class GpuRunner:
             out += conv(hits, n)
         return out, scanned.value
 
+    def fetch_records(self, total):
+        """(key_bytes, address, wif) of every hit of the last scan, formatted by the library in bulk."""
+        out = []
+        stride, chunk = 96, 8192
+        keys = C.create_string_buffer(32 * chunk)
+        addrs = C.create_string_buffer(stride * chunk)
+        wifs = C.create_string_buffer(stride * chunk)
+        while len(out) < total:
+            n = int(self._lib.vgen_cuda_scan_fetch_records(self._ctx, len(out), chunk, keys, addrs, wifs, stride))
+            if n == 0:
+                break
+            kraw, araw, wraw = keys.raw, addrs.raw, wifs.raw
+            for i in range(n):
+                a = araw[stride * i:stride * i + stride]
+                w = wraw[stride * i:stride * i + stride]
+                out.append((kraw[32 * i:32 * i + 32], a[:a.index(0)].decode(), w[:w.index(0)].decode()))
+        return out
+
     def bench_resident(self, start, n_windows):
         ms = C.c_float(0)
         keys = C.c_uint64(0)
         launches = C.c_uint64(0)
         self._check(self._lib.vgen_cuda_bench_resident(self._ctx, _be(start), n_windows, C.byref(ms), C.byref(keys), C.byref(launches)))
         return ms.value, keys.value, launches.value
+
+
+def plan_windows(start, end, global_lanes, lane, sm_count=148, keys_per_launch_hint=0, can_end_early=False):
+    """[(first_key, n_keys)] that global lane `lane` of `global_lanes` scans in [start, end] (vgen_plan_windows; no GPU needed)."""
+    L = _cabi.lib()
+    n = L.vgen_plan_windows(_be(start), _be(end), sm_count, keys_per_launch_hint, global_lanes, lane, int(can_end_early), None, None, 0)
+    if n < 0:
+        raise _cabi.VgenError(int(n), "vgen_plan_windows")
+    keys = C.create_string_buffer(32 * max(n, 1))
+    lens = (C.c_uint64 * max(n, 1))()
+    L.vgen_plan_windows(_be(start), _be(end), sm_count, keys_per_launch_hint, global_lanes, lane, int(can_end_early), keys, lens, n)
+    raw = keys.raw
+    return [(int.from_bytes(raw[32 * i:32 * i + 32], "big"), int(lens[i])) for i in range(n)]
 
 
 class StopFlag:
@@ -180,12 +211,13 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
     runner.set_pattern(pattern, fmt)
     t0 = time.perf_counter()
     count = int(config.count)
-    hits, scanned = runner.scan_raw(start, end, max_hits=count, stop=stop._ptr() if stop is not None else None, progress=progress_cb)
+    # first call with a 1-record buffer: the confirmed hits stay in the context and are formatted in bulk below
+    _, scanned = runner.scan_raw(start, end, max_hits=count, stop=stop._ptr() if stop is not None else None, progress=progress_cb,
+                                 hits_cap=1, fetch_all=False)
+    total = int(runner._lib.vgen_cuda_scan_total_hits(runner._ctx))
     elapsed = time.perf_counter() - t0
-    matches = []
-    for key, digest, _lane in hits:
-        kb = _be(key)
-        matches.append(GeneratedAddress(address=address_from_digest(fmt, digest), wif=wif_from_key(fmt, kb), hex=kb.hex(), format=fmt))
+    matches = [GeneratedAddress(address=a, wif=w, hex=k.hex(), format=fmt) for k, a, w in runner.fetch_records(total)]
+    elapsed = time.perf_counter() - t0
     return ScanResult(matches=matches, operations=scanned, elapsed_secs=elapsed)
 
 
