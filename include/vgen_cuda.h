@@ -89,6 +89,10 @@ uint64_t vgen_cuda_scan_fetch_hits(const vgen_ctx *ctx, uint64_t offset, vgen_hi
  * `stride` (>= 96) bytes per hit. Any of the three outputs may be NULL. Returns the number of hits written. */
 uint64_t vgen_cuda_scan_fetch_records(const vgen_ctx *ctx, uint64_t offset, uint64_t cap, uint8_t *keys32, char *addresses, char *wifs, size_t stride);
 
+/* Same records as text, "<key hex> <address> <wif>\n" per hit, formatted on all host threads; at most max_hits hits and
+ * what fits in cap bytes. Returns the number of bytes written (NUL-terminated), *n_written = hits written. */
+int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t max_hits, char *buf, size_t cap, uint64_t *n_written);
+
 /* generate_batch (src/gpu.rs:660): hash160 of the compressed public key of n sequential scalars, 20 bytes
  * each; zeros for invalid scalars. */
 int vgen_cuda_hash160_batch(vgen_ctx *ctx, const uint8_t start_be[32], uint64_t n, uint8_t *out20);

@@ -4,6 +4,8 @@
 #include <string.h>
 #include <stdio.h>
 #include <new>
+#include <thread>
+#include <algorithm>
 
 struct vgen_ctx {
     vg::Engine engine;
@@ -120,6 +122,37 @@ uint64_t vgen_cuda_scan_fetch_records(const vgen_ctx *ctx, uint64_t offset, uint
         if (wifs) { std::string w = vg::format_wif(fmt, kb); strncpy(wifs + stride * i, w.c_str(), stride - 1); wifs[stride * i + stride - 1] = 0; }
     }
     return n;
+}
+// "<key hex> <address> <wif>\n" per hit, formatted on all host threads (the reference builds these per match with rayon,
+// src/gpu.rs:1030-1093)
+int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t max_hits, char *buf, size_t cap, uint64_t *n_written) {
+    if (!ctx || !buf || !n_written) return VGEN_ERR_INVALID_ARG;
+    *n_written = 0;
+    if (offset >= ctx->hits.size()) { if (cap) buf[0] = 0; return 0; }
+    const int fmt = ctx->engine.pattern().format;
+    const size_t kRec = 64 + 1 + 96 + 1 + 64 + 1;                 // upper bound of one line
+    uint64_t n = std::min<uint64_t>(ctx->hits.size() - offset, max_hits);
+    if (cap < 1) return VGEN_ERR_BUFFER;
+    n = std::min<uint64_t>(n, (cap - 1) / kRec);
+    if (n == 0) return VGEN_ERR_BUFFER;
+    std::vector<std::string> lines(n);
+    unsigned nt = std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)(n / 256 + 1)));
+    auto work = [&](unsigned t) {
+        for (uint64_t i = t; i < n; i += nt) {
+            const vg::Hit &h = ctx->hits[offset + i];
+            uint8_t kb[32]; h.key.to_be(kb);
+            lines[i] = vg::h_hex(kb, 32) + " " + vg::format_address(fmt, h.digest) + " " + vg::format_wif(fmt, kb) + "\n";
+        }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    size_t pos = 0;
+    for (auto &l : lines) { memcpy(buf + pos, l.data(), l.size()); pos += l.size(); }
+    buf[pos] = 0;
+    *n_written = n;
+    return (int64_t)pos;
 }
 int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride) {
     if (!ctx || !start_be || (!out && n)) return VGEN_ERR_INVALID_ARG;

@@ -141,21 +141,16 @@ class GpuRunner:
         return out, scanned.value
 
     def fetch_records(self, total):
-        """(key_bytes, address, wif) of every hit of the last scan, formatted by the library in bulk."""
+        """[(key_hex, address, wif)] of every hit of the last scan, formatted by the library in bulk (vgen_cuda_scan_fetch_text)."""
         out = []
-        stride, chunk = 96, 8192
-        keys = C.create_string_buffer(32 * chunk)
-        addrs = C.create_string_buffer(stride * chunk)
-        wifs = C.create_string_buffer(stride * chunk)
+        cap = 1 << 22
+        buf = C.create_string_buffer(cap)
+        n = C.c_uint64(0)
         while len(out) < total:
-            n = int(self._lib.vgen_cuda_scan_fetch_records(self._ctx, len(out), chunk, keys, addrs, wifs, stride))
-            if n == 0:
+            nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, len(out), total - len(out), buf, cap, C.byref(n)))
+            if nb <= 0 or n.value == 0:
                 break
-            kraw, araw, wraw = keys.raw, addrs.raw, wifs.raw
-            for i in range(n):
-                a = araw[stride * i:stride * i + stride]
-                w = wraw[stride * i:stride * i + stride]
-                out.append((kraw[32 * i:32 * i + 32], a[:a.index(0)].decode(), w[:w.index(0)].decode()))
+            out += [ln.split(" ") for ln in buf.raw[:nb].decode("ascii").splitlines()]
         return out
 
     def bench_resident(self, start, n_windows):
@@ -216,7 +211,7 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
                                  hits_cap=1, fetch_all=False)
     total = int(runner._lib.vgen_cuda_scan_total_hits(runner._ctx))
     elapsed = time.perf_counter() - t0
-    matches = [GeneratedAddress(address=a, wif=w, hex=k.hex(), format=fmt) for k, a, w in runner.fetch_records(total)]
+    matches = [GeneratedAddress(address=a, wif=w, hex=k, format=fmt) for k, a, w in runner.fetch_records(total)]
     elapsed = time.perf_counter() - t0
     return ScanResult(matches=matches, operations=scanned, elapsed_secs=elapsed)
 
