@@ -182,3 +182,18 @@ def test_stop_flag_and_progress(small_runner):
     res = vg.scan_gpu_with_runner(vg.Pattern("^1CatDogs"), cfg, cb, stop, small_runner)
     assert seen == sorted(seen) and len(seen) >= 3
     assert res.operations < (1 << 30)
+
+
+def test_multi_device_context_equals_single(runner):
+    """One context over two GPUs (lanes on different devices, hits merged on the host) == the single-GPU set."""
+    from vgen_b200 import _cabi
+    if _cabi.lib().vgen_cuda_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    start, n = 2**64, runner.batch_size * 5 + 4321
+    single = _scan(runner, "p2pkh", "^1Ca", start, n)
+    r2 = vg.GpuRunner(devices=[0, 1])
+    try:
+        both = _scan(r2, "p2pkh", "^1Ca", start, n)
+    finally:
+        r2.close()
+    assert [m.hex for m in both.matches] == [m.hex for m in single.matches] and both.operations == n

@@ -1,6 +1,7 @@
 """AddressFormat / GeneratedAddress, mirroring src/address.rs:11-72 of the reference. String encoding of a hit
 (address from digest, WIF from key) is done by the library's host layer (vgen_format_address / vgen_format_wif)."""
 import ctypes as C
+import typing
 import enum
 from dataclasses import dataclass
 
@@ -39,8 +40,7 @@ class AddressFormat(enum.IntEnum):
         return AddressFormat(table[s.lower()])
 
 
-@dataclass
-class GeneratedAddress:             # src/address.rs:62-72
+class GeneratedAddress(typing.NamedTuple):      # src/address.rs:62-72 (a tuple type: dense scans build tens of thousands per call)
     address: str
     wif: str
     hex: str

@@ -140,6 +140,7 @@ int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t
     auto work = [&](unsigned t) {
         for (uint64_t i = t; i < n; i += nt) {
             const vg::Hit &h = ctx->hits[offset + i];
+            if (!h.text.empty()) continue;                        // already built by the scan's confirm job
             uint8_t kb[32]; h.key.to_be(kb);
             lines[i] = vg::h_hex(kb, 32) + " " + vg::format_address(fmt, h.digest) + " " + vg::format_wif(fmt, kb) + "\n";
         }
@@ -149,7 +150,10 @@ int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t
     work(0);
     for (auto &x : th) x.join();
     size_t pos = 0;
-    for (auto &l : lines) { memcpy(buf + pos, l.data(), l.size()); pos += l.size(); }
+    for (uint64_t i = 0; i < n; i++) {
+        const std::string &l = lines[i].empty() ? ctx->hits[offset + i].text : lines[i];
+        memcpy(buf + pos, l.data(), l.size()); pos += l.size();
+    }
     buf[pos] = 0;
     *n_written = n;
     return (int64_t)pos;

@@ -9,6 +9,7 @@
 #include "engine.h"
 #include <algorithm>
 #include <deque>
+#include <future>
 #include <string.h>
 
 namespace vg {
@@ -16,6 +17,7 @@ namespace vg {
 #define CK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { err = std::string(#call) + ": " + cudaGetErrorString(e_); return false; } } while (0)
 
 static const int kCounterWords = 4;
+static const uint32_t kEagerTextHits = 1u << 16;   // windows with at most this many device hits get their text records built by the confirm job
 
 Engine::~Engine() { destroy(); }
 
@@ -242,6 +244,15 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         inflight.push_back({li, s});
         return true;
     };
+    std::deque<std::future<std::vector<Hit>>> pending;   // per-window confirm jobs, in window order
+    auto drain = [&](bool only_ready) {
+        while (!pending.empty()) {
+            if (only_ready && pending.front().wait_for(std::chrono::seconds(0)) == std::future_status::timeout) break;
+            std::vector<Hit> v = pending.front().get();
+            pending.pop_front();
+            for (auto &h : v) hits.push_back(std::move(h));
+        }
+    };
     auto collect = [&](uint32_t li, int s, bool keep) -> bool {
         Lane &L = lanes_[li]; Slot &S = L.slot[s];
         CK(cudaSetDevice(L.device));
@@ -267,26 +278,43 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         }
         uint64_t cap = levels_[S.level].window;
         if (n_hits > cap) n_hits = (uint32_t)cap;         // cannot happen: at most one hit per key
-        size_t before = hits.size();
+        // device records -> host vector (pinned staging is reused by the next window), then confirm (+ format when the
+        // window is sparse) on a worker thread so that it overlaps the windows still running on the GPU
+        auto recs = std::make_shared<std::vector<vg_hit_rec>>();
+        recs->reserve(n_hits);
         for (uint32_t done = 0; done < n_hits;) {
             uint32_t chunk = (uint32_t)std::min<size_t>(n_hits - done, L.h_hits_cap);
             CK(cudaMemcpyAsync(L.h_hits, S.d_hits + done, (size_t)chunk * sizeof(vg_hit_rec), cudaMemcpyDeviceToHost, L.copy_stream));
             CK(cudaStreamSynchronize(L.copy_stream));
             d2h_bytes += (uint64_t)chunk * sizeof(vg_hit_rec);
-            for (uint32_t i = 0; i < chunk; i++) {
-                const vg_hit_rec &R = L.h_hits[i];
+            recs->insert(recs->end(), L.h_hits, L.h_hits + chunk);
+            done += chunk;
+        }
+        const U256 base = S.base;
+        const bool with_text = n_hits <= kEagerTextHits;
+        auto job = [this, recs, base, li, fmt, with_text]() {
+            std::vector<Hit> out;
+            out.reserve(recs->size());
+            for (const vg_hit_rec &R : *recs) {
                 Hit h; memset(h.digest, 0, 32);
                 h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = li;
                 for (int w = 0; w < 8; w++) for (int b = 0; b < 4; b++) h.digest[4 * w + b] = (uint8_t)(R.digest[w] >> (8 * b));
                 // exact confirmation on the host: re-encode the address from the digest and run the full DFA
                 std::string addr = format_address(fmt, h.digest);
                 if (!lp_.dfa.match(addr.data(), addr.size())) continue;
-                h.key = S.base.add64(((uint64_t)R.idx_hi << 32) | R.idx_lo);
-                hits.push_back(h);
+                h.key = base.add64(((uint64_t)R.idx_hi << 32) | R.idx_lo);
+                if (with_text) {
+                    uint8_t kb[32]; h.key.to_be(kb);
+                    h.text = h_hex(kb, 32) + " " + addr + " " + format_wif(fmt, kb) + "\n";
+                }
+                out.push_back(std::move(h));
             }
-            done += chunk;
-        }
-        std::sort(hits.begin() + before, hits.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
+            std::sort(out.begin(), out.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
+            return out;
+        };
+        pending.push_back(std::async(recs->size() >= 64 ? std::launch::async : std::launch::deferred, job));
+        if (max_hits) drain(false);                       // a hit limit needs the confirmed count now
+        else drain(true);                                  // otherwise only reap the jobs that are already finished
         keys_scanned += S.limit;
         return true;
     };
@@ -303,6 +331,7 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         }
         if (!stopping && !issue(li)) return false;
     }
+    drain(false);
     for (auto &L : lanes_) { CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); L.centers_level = -1; }
     std::sort(hits.begin(), hits.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
     if (max_hits && hits.size() > max_hits) hits.resize(max_hits);

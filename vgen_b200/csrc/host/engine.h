@@ -12,7 +12,8 @@
 
 namespace vg {
 
-struct Hit { U256 key; uint8_t digest[32]; uint32_t digest_len; uint32_t lane; };
+// text: "<key hex> <address> <wif>\n", filled by the per-window confirm job when the window is sparse (else empty: formatted on demand)
+struct Hit { U256 key; uint8_t digest[32]; uint32_t digest_len; uint32_t lane; std::string text; };
 
 struct Slot {                 // one of the two windows a lane keeps in flight
     vg_hit_rec *d_hits = nullptr;

@@ -3,6 +3,7 @@
 there is no CPU fallback: if the library or a B200 is missing, construction raises."""
 import ctypes as C
 import enum
+import itertools
 import secrets
 import time
 
@@ -141,17 +142,18 @@ class GpuRunner:
         return out, scanned.value
 
     def fetch_records(self, total):
-        """[(key_hex, address, wif)] of every hit of the last scan, formatted by the library in bulk (vgen_cuda_scan_fetch_text)."""
-        out = []
+        """(key_hex[], address[], wif[]) of every hit of the last scan, formatted by the library (vgen_cuda_scan_fetch_text)."""
+        toks, got = [], 0
         cap = 1 << 22
         buf = C.create_string_buffer(cap)
         n = C.c_uint64(0)
-        while len(out) < total:
-            nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, len(out), total - len(out), buf, cap, C.byref(n)))
+        while got < total:
+            nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, got, total - got, buf, cap, C.byref(n)))
             if nb <= 0 or n.value == 0:
                 break
-            out += [ln.split(" ") for ln in buf.raw[:nb].decode("ascii").splitlines()]
-        return out
+            toks += C.string_at(buf, nb).decode("ascii").split()
+            got += n.value
+        return toks[0::3], toks[1::3], toks[2::3]
 
     def bench_resident(self, start, n_windows):
         ms = C.c_float(0)
@@ -211,7 +213,8 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
                                  hits_cap=1, fetch_all=False)
     total = int(runner._lib.vgen_cuda_scan_total_hits(runner._ctx))
     elapsed = time.perf_counter() - t0
-    matches = [GeneratedAddress(address=a, wif=w, hex=k, format=fmt) for k, a, w in runner.fetch_records(total)]
+    keys, addrs, wifs = runner.fetch_records(total)
+    matches = list(map(GeneratedAddress, addrs, wifs, keys, itertools.repeat(fmt)))
     elapsed = time.perf_counter() - t0
     return ScanResult(matches=matches, operations=scanned, elapsed_secs=elapsed)
 
