@@ -4,7 +4,7 @@
 #define VG_HOST_EMU 1
 #include <vector>
 #include <cstring>
-#include "../../vgen_b200/csrc/match.cuh"
+#include "../../vgen_b200/csrc/taproot.cuh"
 
 static const uint32_t G_XY[16] = {
     0x16F81798, 0x59F2815B, 0x2DCE28D9, 0x029BFCDB, 0xCE870B07, 0x55A06295, 0xF9DCBBAC, 0x79BE667E,
@@ -37,8 +37,32 @@ int emu_confirm(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_
     vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
     switch (fmt) {
         case 0: return vg_confirm<0>(m, dv, dg); case 1: return vg_confirm<1>(m, dv, dg); case 2: return vg_confirm<2>(m, dv, dg);
-        case 3: return vg_confirm<3>(m, dv, dg); default: return vg_confirm<5>(m, dv, dg);
+        case 3: return vg_confirm<3>(m, dv, dg); case 4: return vg_confirm<4>(m, dv, dg); default: return vg_confirm<5>(m, dv, dg);
     }
+}
+// P2TR stage 2 (taproot.cuh) over n keys (n a multiple of VG_TAP_GROUP) whose even-Y internal keys are in points[16*n]:
+// writes the 32-byte witness programs. bits = window width of the fixed-base table (4 keeps the host build cheap).
+static std::vector<uint32_t> g_tap; static uint32_t g_tap_bits = 0;
+void emu_tap_stage2(uint32_t *points, uint32_t n, uint32_t bits, uint8_t *out32) {
+    ensure_pow2();
+    if (g_tap_bits != bits) {
+        const size_t cnt = (size_t)(256 / bits) << bits;
+        g_tap.assign(cnt * 16, 0);
+        for (size_t i = 0; i < cnt; i++) {
+            uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1u << bits) - 1)), k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            if (!v) continue;
+            k[(j * bits) >> 5] = v << ((j * bits) & 31u);
+            fe x, y; scalar_mul_pow2(x, y, k, g_pow2.data());
+            memcpy(&g_tap[i * 16], x.v, 32); memcpy(&g_tap[i * 16 + 8], y.v, 32);
+        }
+        g_tap_bits = bits;
+    }
+    vg_scan_params P; memset(&P, 0, sizeof P);
+    uint32_t hitc = 0;
+    P.points = points; P.tap_table = g_tap.data(); P.tap_bits = bits; P.limit = n; P.dump = out32; P.dump_stride = 32; P.hit_count = &hitc;
+    vg_dfa_view dv; dv.table = nullptr; dv.accept = nullptr; dv.sym = nullptr;
+    memset(out32, 0, (size_t)n * 32);
+    for (uint32_t g = 0; g < n / VG_TAP_GROUP; g++) vg_tap_thread<VG_MODE_DUMP>(P, dv, (unsigned long long)g * VG_TAP_GROUP);
 }
 void emu_keccak_hex40(const uint32_t *m, uint32_t *out) { keccak_hex40(out, m); }
 
@@ -65,6 +89,8 @@ int emu_walk_dump(int fmt, const uint32_t *start, uint32_t T, uint32_t H, uint32
     P.n_threads = T; P.half = H; P.centers = centers.data(); P.scratch = scratch.data(); P.gtab = gtab.data();
     P.limit = W; P.hit_count = &hitc; P.degen_count = &degc; P.degen_list = degl.data(); P.degen_cap = T;
     P.dump_stride = stride;
+    std::vector<uint32_t> points(fmt == 4 ? (size_t)W * 16 : 0);
+    P.points = points.data();
     vg_dfa_view dv; dv.table = nullptr; dv.accept = nullptr; dv.sym = nullptr;
     for (uint32_t w = 0; w < n_windows; w++) {
         P.dump = out + (size_t)w * W * stride;
@@ -77,6 +103,7 @@ int emu_walk_dump(int fmt, const uint32_t *start, uint32_t T, uint32_t H, uint32
                 default: vg_walk_thread<5, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
             }
         }
+        if (fmt == 4) emu_tap_stage2(points.data(), (uint32_t)W, 4, P.dump);      // stride must be 32
     }
     return (int)degc;
 }

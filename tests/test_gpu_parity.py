@@ -75,6 +75,15 @@ def test_digest_batch_all_formats(small_runner, fmt):
         assert got == want, (fmt, start)
 
 
+def test_p2tr_digest_batch_is_the_witness_program(small_runner):
+    """P2TR: both stages on the GPU (even-Y internal key, TapTweak, + t*G) == the oracle's output key (src/address.rs:136-140)."""
+    rng = random.Random(7)
+    for start, n in ((1, 5000), (rng.randrange(1, N - 10**6), 20000), (N - 3000, 4000), (2**64, small_runner.batch_size + 777)):
+        got = small_runner.digest_batch("p2tr", start, n)
+        want = oracle.digest_batch("p2tr", start, n)
+        assert got == want, start
+
+
 def test_multi_window_walk_consistency(small_runner):
     # 3+ windows of the small runner: the next-centre update (C + W*G) is exercised
     n = small_runner.batch_size * 3 + 777
@@ -107,6 +116,7 @@ def _check_scan(runner, fmt, pat, start, n, ci=False):
     ("p2pkh-uncompressed", "^1Ab", False), ("p2sh-p2wpkh", "^3Ab", False), ("p2sh-p2wpkh", "^3", False),
     ("p2wpkh", "^bc1qaa", False), ("p2wpkh", "dead$", False), ("p2wpkh", "aa.*zz", False),
     ("ethereum", "^0xdea", False), ("ethereum", "^0xDe", False), ("ethereum", "^0xab", True), ("ethereum", "F00$", False),
+    ("p2tr", "^bc1pqq", False), ("p2tr", "dead$", False), ("p2tr", "^bc1p.*zzz", False), ("p2tr", "^bc1q", False),
     ("p2pkh", "abc$", False), ("p2pkh", "[0-9]{4}$", False), ("p2pkh", "^1.*XYZ", False), ("p2pkh", "^3", False),
 ])
 def test_scan_match_sets_small(small_runner, fmt, pat, ci):
@@ -143,6 +153,16 @@ def test_scan_exact_address_planted(runner):
     assert [int(m.hex, 16) for m in res.matches] == [start + off]
     assert res.matches[0].address == addr and res.operations == n
     assert runner.matcher_kind() == "exact"
+
+
+def test_p2tr_exact_address_planted(small_runner):
+    start = 2**65
+    n = small_runner.batch_size * 2 + 345
+    off = int(0.61 * n)
+    addr = oracle.address("p2tr", start + off)[0]
+    res = _scan(small_runner, "p2tr", "^" + addr + "$", start, n)
+    assert [int(m.hex, 16) for m in res.matches] == [start + off] and res.matches[0].address == addr and res.operations == n
+    assert small_runner.matcher_kind() == "exact"
 
 
 def test_config_c1_full_match_set(runner):

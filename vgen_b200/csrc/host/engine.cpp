@@ -29,11 +29,12 @@ void Engine::destroy() {
             if (S.d_hits) cudaFree(S.d_hits);
             if (S.d_counters) cudaFree(S.d_counters);
             if (S.d_degen) cudaFree(S.d_degen);
+            if (S.d_base8) cudaFree(S.d_base8);
             if (S.h_counters) cudaFreeHost(S.h_counters);
             if (S.done) cudaEventDestroy(S.done);
         }
         for (void *p : {(void *)L.d_pow2, (void *)L.d_gtab, (void *)L.d_centers, (void *)L.d_scratch, (void *)L.d_base8,
-                        (void *)L.d_stride_pts, (void *)L.d_dfa_table, (void *)L.d_dfa_accept})
+                        (void *)L.d_stride_pts, (void *)L.d_points, (void *)L.d_tap_table, (void *)L.d_dfa_table, (void *)L.d_dfa_accept})
             if (p) cudaFree(p);
         if (L.h_hits) cudaFreeHost(L.h_hits);
         if (L.own_stream && L.stream) cudaStreamDestroy(L.stream);
@@ -76,6 +77,7 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
             CK(cudaMalloc(&S.d_hits, (size_t)F.window * sizeof(vg_hit_rec)));
             CK(cudaMalloc(&S.d_counters, kCounterWords * 4));
             CK(cudaMalloc(&S.d_degen, (size_t)F.threads * 4));
+            CK(cudaMalloc(&S.d_base8, 32));
             CK(cudaHostAlloc(&S.h_counters, kCounterWords * 4, cudaHostAllocDefault));
             CK(cudaEventCreateWithFlags(&S.done, cudaEventDisableTiming));
         }
@@ -118,11 +120,30 @@ bool Engine::upload_dfa(std::string &err) {
     return true;
 }
 
+static const uint32_t kTapBits = 16;     // 16 windows of 16 bits: 16 x 65536 x 64 B = 64 MiB, resident in the 126 MB L2
+
+// P2TR needs two more buffers per lane: the stage-1 -> stage-2 point buffer (64 B per window key) and the
+// fixed-base table of the tweak addition. Allocated and built on first use.
+bool Engine::ensure_taproot(std::string &err) {
+    const Level &F = levels_.back();
+    for (auto &L : lanes_) {
+        if (L.d_tap_table) continue;
+        CK(cudaSetDevice(L.device));
+        CK(cudaMalloc(&L.d_points, (size_t)F.window * 64));
+        CK(cudaMalloc(&L.d_tap_table, ((size_t)(256 / kTapBits) << kTapBits) * 64));
+        CK(launch_build_tap_table(L.d_tap_table, kTapBits, L.d_pow2, L.stream));
+        launches++;
+        CK(cudaStreamSynchronize(L.stream));
+    }
+    return true;
+}
+
 bool Engine::set_pattern(int format, const std::string &pattern, bool ci, std::string &err) {
     LoweredPattern lp;
     if (!lower_pattern(format, pattern, ci, lp, err)) return false;
     lp_ = lp;
     has_pattern_ = true;
+    if (format == VG_FMT_P2TR && !ensure_taproot(err)) return false;
     return upload_dfa(err);
 }
 
@@ -169,6 +190,7 @@ void Engine::fill_params(Lane &L, Slot &S, vg_scan_params &P) {
     P.limit = S.limit;
     P.hits = S.d_hits; P.hit_count = S.d_counters; P.hit_cap = (uint32_t)std::min<uint64_t>(V.window, 0xffffffffu);
     P.degen_list = S.d_degen; P.degen_count = S.d_counters + 1; P.degen_cap = V.threads;
+    P.points = L.d_points; P.tap_table = L.d_tap_table; P.tap_bits = kTapBits;
     P.m = lp_.dev;
     P.m.dfa.table = L.d_dfa_table; P.m.dfa.accept = L.d_dfa_accept;
     P.dfa_smem_bytes = (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa) ? dfa_smem_bytes(P.m.dfa) : 0;
@@ -181,6 +203,14 @@ bool Engine::launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uin
     CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
     CK(launch_walk(fmt, mode, P, levels_[S.level].blocks, L.stream));
     launches++; h2d_bytes += sizeof(vg_scan_params);            // kernel parameters travel with the launch
+    if (fmt == VG_FMT_P2TR) {
+        // stage 1 wrote the internal keys; redo flagged batches on the device (count read there), then the tweak stage
+        uint32_t k8[8]; S.base.to_limbs32(k8);
+        CK(cudaMemcpyAsync(S.d_base8, k8, 32, cudaMemcpyHostToDevice, L.stream));
+        CK(launch_slow(fmt, mode, P, S.d_base8, L.d_pow2, 0xffffffffu, L.stream));
+        CK(launch_taptweak(mode, P, L.stream));
+        launches += 2; h2d_bytes += 32 + 2 * sizeof(vg_scan_params);
+    }
     CK(cudaMemcpyAsync(S.h_counters, S.d_counters, kCounterWords * 4, cudaMemcpyDeviceToHost, L.stream));
     d2h_bytes += kCounterWords * 4;
     CK(cudaEventRecord(S.done, L.stream));
@@ -196,7 +226,6 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
                   std::vector<Hit> &hits, uint64_t &keys_scanned, std::string &err) {
     hits.clear(); keys_scanned = 0;
     if (!has_pattern_) { err = "no pattern set"; return false; }
-    if (lp_.format == VG_FMT_P2TR) { err = "P2TR is not supported by the CUDA scan path yet"; return false; }
     // valid scalars are 1..n-1 (src/address.rs:93); scalars outside are skipped, not counted (src/scanner.rs:294-295)
     U256 start = start_in, end = end_in ? *end_in : secp_order_minus1();
     if (end_in && end < start) { err = "range end is below range start"; return false; }
@@ -260,7 +289,11 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         S.busy = false;
         if (!keep) return true;
         uint32_t n_hits = S.h_counters[0], n_degen = S.h_counters[1];
-        if (n_degen) {
+        if (n_degen && fmt == VG_FMT_P2TR) {
+            // already redone on the device between the two stages (launch_window); only the centres need a new set-up
+            L.centers_level = -1;
+            runs[li].have_expect = false;
+        } else if (n_degen) {
             // batches that touched the point at infinity or collided with a table point: redo them key by key
             vg_scan_params P; fill_params(L, S, P);
             uint32_t k8[8]; S.base.to_limbs32(k8);
@@ -348,6 +381,7 @@ bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *ou
         U256 room = secp_order_minus1().sub(start).add64(1);
         if (room.fits64() && room.w[0] < n) n = room.w[0];
     }
+    if (format == VG_FMT_P2TR && !ensure_taproot(err)) return false;
     Lane &L = lanes_[0];
     CK(cudaSetDevice(L.device));
     uint32_t saved_idx = shard_index_, saved_cnt = shard_count_;
@@ -381,7 +415,9 @@ bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *ou
         if (good) good = launch_window(L0, 0, format, VG_MODE_DUMP, d_out + off * stride, stride, err);
         if (good && cudaStreamSynchronize(L0.stream) != cudaSuccess) { err = "walk kernel failed"; good = false; }
         S.busy = false;
-        if (good && S.h_counters[1]) {
+        if (good && S.h_counters[1] && format == VG_FMT_P2TR) {
+            if (off + W < n) good = setup_centers(L0, level, base.add64(W), err);      // flagged batches were redone on the device
+        } else if (good && S.h_counters[1]) {
             vg_scan_params P; fill_params(L0, S, P);
             P.dump = d_out + off * stride; P.dump_stride = stride;
             uint32_t k8[8]; base.to_limbs32(k8);
@@ -419,6 +455,7 @@ bool Engine::bench_resident(const U256 &start, uint32_t n_windows, float &ms, ui
     for (uint32_t w = 0; w < n_windows; w++) {
         CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
         CK(launch_walk(lp_.format, VG_MODE_MATCH, P, levels_[fl].blocks, L.stream));
+        if (lp_.format == VG_FMT_P2TR) { CK(launch_taptweak(VG_MODE_MATCH, P, L.stream)); launches++; }
     }
     CK(cudaEventRecord(e1, L.stream));
     CK(cudaEventSynchronize(e1));

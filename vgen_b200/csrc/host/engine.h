@@ -19,6 +19,7 @@ struct Slot {                 // one of the two windows a lane keeps in flight
     vg_hit_rec *d_hits = nullptr;
     uint32_t *d_counters = nullptr;    // [0] hit_count, [1] degen_count
     uint32_t *d_degen = nullptr;
+    uint32_t *d_base8 = nullptr;       // window base scalar for the device-chained slow pass (P2TR)
     uint32_t *h_counters = nullptr;    // pinned
     cudaEvent_t done = nullptr;
     bool busy = false;
@@ -34,6 +35,7 @@ struct Lane {
     bool own_stream = true;
     int sm_count = 0;
     uint32_t *d_pow2 = nullptr, *d_gtab = nullptr, *d_centers = nullptr, *d_scratch = nullptr, *d_base8 = nullptr;
+    uint32_t *d_points = nullptr, *d_tap_table = nullptr;   // P2TR only, allocated on first use (taproot.cuh)
     uint32_t *d_stride_pts = nullptr;          // [n_levels][16] scratch for stride points
     uint16_t *d_dfa_table = nullptr; uint8_t *d_dfa_accept = nullptr;
     vg_hit_rec *h_hits = nullptr; size_t h_hits_cap = 0;   // pinned staging
@@ -73,6 +75,7 @@ private:
     bool launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uint32_t dump_stride, std::string &err);
     void fill_params(Lane &L, Slot &S, vg_scan_params &P);
     bool upload_dfa(std::string &err);
+    bool ensure_taproot(std::string &err);
     void destroy();
     std::vector<Lane> lanes_;
     std::vector<Level> levels_;

@@ -140,6 +140,31 @@ VG_DEV bool vg_match_p2wpkh(const vg_matcher_dev &m, const vg_dfa_view &v, const
     return v.accept[st] != 0;
 }
 
+// Bech32m segwit v1 address of a 32-byte program (P2TR, BIP350): "bc1p" is pre-consumed by the host, then 52 data symbols
+// (256 bits + 4 zero pad bits) and 6 checksum symbols. dg = the program bytes as little-endian words.
+VG_DEV bool vg_match_p2tr(const vg_matcher_dev &m, const vg_dfa_view &v, const uint32_t dg[VG_DIGEST_WORDS]) {
+    uint32_t B[9];
+    VG_UNROLL for (int i = 0; i < 8; i++) B[i] = vg_bswap(dg[i]);
+    B[8] = 0;
+    uint32_t chk = 1;
+    {   // hrp expand of "bc" = 3,3,0,2,3 then witness version 1
+        const uint32_t pre[6] = {3, 3, 0, 2, 3, 1};
+        VG_UNROLL for (int i = 0; i < 6; i++) chk = vg_bech32_polymod_step(chk, pre[i]);
+    }
+    const uint32_t nc = m.dfa.n_classes;
+    uint32_t st = m.dfa.start;
+    VG_UNROLL for (int j = 0; j < 52; j++) {
+        const int bit = 5 * j, wi = bit >> 5, off = bit & 31;
+        uint32_t val = off <= 27 ? (B[wi] >> (27 - off)) & 31u : ((B[wi] << (off - 27)) | (B[wi + 1] >> (59 - off))) & 31u;
+        chk = vg_bech32_polymod_step(chk, val);
+        st = vg_dfa_step(v, nc, st, v.sym[val]);
+    }
+    VG_UNROLL for (int i = 0; i < 6; i++) chk = vg_bech32_polymod_step(chk, 0);
+    chk ^= 0x2bc830a3u;
+    VG_UNROLL for (int i = 0; i < 6; i++) st = vg_dfa_step(v, nc, st, v.sym[(chk >> (5 * (5 - i))) & 31u]);
+    return v.accept[st] != 0;
+}
+
 // Ethereum: "0x" pre-consumed by the host; 40 hex symbols in EIP-55 case (symbol = nibble, +16 when upper-cased).
 // When the DFA does not distinguish a-f from A-F (m.dfa.flags bit 0 clear) the checksum Keccak is skipped.
 VG_DEV bool vg_match_eth(const vg_matcher_dev &m, const vg_dfa_view &v, const uint32_t dg[VG_DIGEST_WORDS]) {
@@ -180,5 +205,5 @@ VG_DEV bool vg_confirm(const vg_matcher_dev &m, const vg_dfa_view &v, const uint
     if (FMT == VG_FMT_P2SH_P2WPKH) return vg_match_base58check<5>(m, v, dg);
     if (FMT == VG_FMT_P2WPKH) return vg_match_p2wpkh(m, v, dg);
     if (FMT == VG_FMT_ETHEREUM) return vg_match_eth(m, v, dg);
-    return true;   // P2TR: the scan path does not run on the device yet (engine rejects it)
+    return vg_match_p2tr(m, v, dg);
 }

@@ -118,6 +118,15 @@ VG_DEV void vg_finish_point(const vg_scan_params &P, const vg_dfa_view &dv, cons
 template <int FMT, int MODE>
 VG_DEV void vg_process_point(const vg_scan_params &P, const vg_dfa_view &dv, fe &x, fe &y, unsigned long long idx, bool valid) {
     fe_canon(x); fe_canon(y);
+    if (FMT == VG_FMT_P2TR) {
+        // stage 1 of the P2TR path: hand the even-Y internal key to stage 2 (taproot.cuh); MODE is applied there
+        valid = valid && idx < P.limit;
+        fe ny; fe_neg(ny, y); fe_canon(ny);
+        const bool odd = (y.v[0] & 1u) != 0;
+        uint32_t *o = P.points + idx * 16;
+        VG_UNROLL for (int l = 0; l < 8; l++) { o[l] = valid ? x.v[l] : 0u; o[8 + l] = valid ? (odd ? ny.v[l] : y.v[l]) : 0u; }
+        return;
+    }
     uint32_t dg[VG_DIGEST_WORDS];
     vg_digest_of_point<FMT>(dg, x, y);
     vg_finish_point<FMT, MODE>(P, dv, dg, idx, valid);

@@ -35,12 +35,32 @@ __global__ void k_build_gtab(uint32_t *gtab, uint32_t half, const uint32_t *pow2
     for (int l = 0; l < 8; l++) { gtab[i * 16 + l] = x.v[l]; gtab[i * 16 + 8 + l] = y.v[l]; }
 }
 
+// tab[j][v][16] = (v << (bits*j)) * G for the P2TR tweak addition; v = 0 entries are never read (all-zero)
+__global__ void k_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2) {
+    const unsigned long long n = (256ull / bits) << bits;
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1ull << bits) - 1));
+    uint32_t k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t bit = j * bits;
+    k[bit >> 5] = v << (bit & 31u);                 // bits divides 32: a digit never straddles a limb
+    fe x, y;
+    bool ok = v != 0 && scalar_mul_pow2(x, y, k, pow2);
+    if (!ok) { fe_set_zero(x); fe_set_zero(y); }
+    for (int l = 0; l < 8; l++) { tab[i * 16 + l] = x.v[l]; tab[i * 16 + 8 + l] = y.v[l]; }
+}
+
 #define VG_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
 cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, cudaStream_t s) {
     k_build_pow2<<<1, 32, 0, s>>>(pow2);
     VG_CK(cudaGetLastError());
     k_build_gtab<<<(half + 127) / 128, 128, 0, s>>>(gtab, half, pow2);
+    return cudaGetLastError();
+}
+cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2, cudaStream_t s) {
+    const unsigned long long n = (256ull / bits) << bits;
+    k_build_tap_table<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(tab, bits, pow2);
     return cudaGetLastError();
 }
 cudaError_t launch_points_of_scalars(uint32_t *out, uint32_t n, const uint32_t *base8_dev, unsigned long long step,

@@ -41,6 +41,9 @@ struct vg_scan_params {
     uint32_t *degen_list; uint32_t *degen_count; uint32_t degen_cap;
     uint32_t dfa_smem_bytes;  // shared-memory bytes for the DFA table + accept flags (0: read them from global memory)
     uint8_t *dump; uint32_t dump_stride;   // VG_MODE_DUMP: digest bytes per key index
+    // P2TR only (taproot.cuh): stage 1 writes the even-Y internal key of window key i to points[16*i .. 16*i+15]
+    // (x limbs, y limbs; all-zero = invalid), stage 2 adds t*G from tap_table[256/tap_bits][1 << tap_bits][16]
+    uint32_t *points; const uint32_t *tap_table; uint32_t tap_bits;
     vg_matcher_dev m;
 };
 

@@ -1,0 +1,124 @@
+// P2TR (BIP341 key-path output, no script tree) on the device: second stage of the scan for VG_FMT_P2TR.
+//
+// The reference's GPU path stops at the even-Y internal key (src/shaders/search_p2tr.wgsl:104-113) and leaves the
+// TapTweak to the host: per key a tagged SHA-256 and a full scalar multiplication through
+// bitcoin::Address::p2tr (src/gpu.rs:1288-1290, src/address.rs:136-140). Here the whole derivation runs on the GPU:
+//
+//   stage 1 (walk kernel, FMT = P2TR): writes the even-Y internal key P = (x, y) of every key of the window into
+//           `points` (64 B per key, limb order as `fe`), all-zero for keys that are invalid / outside the range;
+//   stage 2 (this file): t = SHA256(SHA256("TapTweak") || SHA256("TapTweak") || x)   [one compression from a
+//           precomputed midstate, same constant as src/shaders/sha256.wgsl:177-249]
+//           Q = P + t*G through a fixed-base table tab[j][v] = v * 2^(bits*j) * G (bits = 16: 16 mixed additions,
+//           64 MiB, L2-resident), kept in Jacobian form; one field inversion per VG_TAP_GROUP keys (Montgomery's
+//           trick over the group's Z^2) turns X/Z^2 into the 32-byte witness program x(Q), which goes through the
+//           same matcher as the other formats (interval / exact / Bech32m-fed DFA).
+#pragma once
+#include "match.cuh"
+
+#ifndef VG_TAP_GROUP
+#define VG_TAP_GROUP 8          // keys handled by one stage-2 thread = keys sharing one field inversion
+#endif
+
+// t as 8 big-endian words (t[0] most significant) of the TapTweak tagged hash of the x-only key
+VG_DEV void vg_taptweak_hash(uint32_t t[8], const fe &x) {
+    const uint32_t mid[8] = {0xd129a2f3u, 0x701c655du, 0x6583b6c3u, 0xb9419727u, 0x95f4e232u, 0x94fd54f4u, 0xa2ae8d85u, 0x47ca590bu};
+    uint32_t w[16];
+    VG_UNROLL for (int i = 0; i < 8; i++) { t[i] = mid[i]; w[i] = x.v[7 - i]; }
+    w[8] = 0x80000000u;
+    VG_UNROLL for (int i = 9; i < 15; i++) w[i] = 0;
+    w[15] = 96 * 8;
+    sha256_compress<0xFF00u>(t, w);
+}
+// t < n ?  (t big-endian words)
+VG_DEV bool vg_tweak_is_valid(const uint32_t t[8]) {
+    uint32_t k[8];
+    VG_UNROLL for (int i = 0; i < 8; i++) k[i] = t[7 - i];
+    uint32_t any = 0;
+    VG_UNROLL for (int i = 0; i < 8; i++) any |= k[i];
+    return any == 0 || scalar_is_valid(k);          // t == 0 is allowed by BIP341 (Q = P)
+}
+// Q = P + t*G in Jacobian coordinates. Returns false when Q is the point at infinity (t*G = -P).
+// gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
+VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
+    q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
+    const uint32_t n_win = 256u / bits, mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
+#ifndef VG_HOST_EMU
+    #pragma unroll 1
+#endif
+    for (uint32_t j = 0; j < n_win; j++) {
+        const uint32_t bit = j * bits;
+        // bit position counted from the least significant end of t; word 7 is the least significant
+        uint32_t word = 0;
+        VG_UNROLL for (int i = 0; i < 8; i++) word = ((bit >> 5) == (uint32_t)i) ? t[7 - i] : word;
+        const uint32_t v = (word >> (bit & 31u)) & mask;
+        if (v == 0) continue;
+        const uint32_t *e = tab + ((size_t)j * ((size_t)mask + 1) + v) * 16;
+        fe bx, by;
+#ifdef VG_HOST_EMU
+        for (int l = 0; l < 8; l++) { bx.v[l] = e[l]; by.v[l] = e[8 + l]; }
+#else
+        const uint4 *e4 = (const uint4 *)e;
+        uint4 a0 = __ldg(e4), a1 = __ldg(e4 + 1), a2 = __ldg(e4 + 2), a3 = __ldg(e4 + 3);
+        bx.v[0] = a0.x; bx.v[1] = a0.y; bx.v[2] = a0.z; bx.v[3] = a0.w; bx.v[4] = a1.x; bx.v[5] = a1.y; bx.v[6] = a1.z; bx.v[7] = a1.w;
+        by.v[0] = a2.x; by.v[1] = a2.y; by.v[2] = a2.z; by.v[3] = a2.w; by.v[4] = a3.x; by.v[5] = a3.y; by.v[6] = a3.z; by.v[7] = a3.w;
+#endif
+        gej_t r;
+        gej_add_affine(r, q, bx, by);
+        q = r;
+    }
+    return !q.inf;
+}
+
+// stage-2 thread: keys [first, first + VG_TAP_GROUP) of the window
+template <int MODE>
+VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsigned long long first) {
+    // X_k, Z_k^2 and the running product Z_0^2 ... Z_k^2 (local memory: indexed by the loop counter)
+    fe X[VG_TAP_GROUP], Z2[VG_TAP_GROUP], pre[VG_TAP_GROUP];
+    uint32_t ok_mask = 0;
+    fe run; fe_set_one(run);
+#ifndef VG_HOST_EMU
+    #pragma unroll 1
+#endif
+    for (int k = 0; k < VG_TAP_GROUP; k++) {
+        const uint32_t *p = P.points + (first + (unsigned long long)k) * 16;
+        fe px, py;
+#ifdef VG_HOST_EMU
+        for (int l = 0; l < 8; l++) { px.v[l] = p[l]; py.v[l] = p[8 + l]; }
+#else
+        const uint4 *p4 = (const uint4 *)p;
+        uint4 a0 = p4[0], a1 = p4[1], a2 = p4[2], a3 = p4[3];
+        px.v[0] = a0.x; px.v[1] = a0.y; px.v[2] = a0.z; px.v[3] = a0.w; px.v[4] = a1.x; px.v[5] = a1.y; px.v[6] = a1.z; px.v[7] = a1.w;
+        py.v[0] = a2.x; py.v[1] = a2.y; py.v[2] = a2.z; py.v[3] = a2.w; py.v[4] = a3.x; py.v[5] = a3.y; py.v[6] = a3.z; py.v[7] = a3.w;
+#endif
+        bool ok = !(fe_is_zero_raw(px) && fe_is_zero_raw(py));
+        fe z2; fe_set_one(z2);
+        fe_set_zero(X[k]);
+        if (ok) {
+            uint32_t t[8];
+            vg_taptweak_hash(t, px);
+            ok = vg_tweak_is_valid(t);
+            gej_t q;
+            if (ok) ok = vg_tap_output_key(q, px, py, t, P.tap_table, P.tap_bits);
+            if (ok) { X[k] = q.x; fe_sqr(z2, q.z); }
+        }
+        if (ok) ok_mask |= 1u << k;
+        Z2[k] = z2;
+        fe_mul(run, run, z2);
+        pre[k] = run;
+    }
+    fe inv;
+    fe_inv(inv, run);                                   // 1 / (Z_0^2 ... Z_{G-1}^2)
+#ifndef VG_HOST_EMU
+    #pragma unroll 1
+#endif
+    for (int k = VG_TAP_GROUP - 1; k >= 0; k--) {
+        fe zi2, xq;
+        if (k > 0) { fe_mul(zi2, inv, pre[k - 1]); fe_mul(inv, inv, Z2[k]); }   // 1/Z_k^2, then inv -> 1/pre[k-1]
+        else zi2 = inv;
+        fe_mul(xq, X[k], zi2);
+        fe_canon(xq);
+        uint32_t dg[VG_DIGEST_WORDS];
+        VG_UNROLL for (int i = 0; i < 8; i++) dg[i] = vg_bswap(xq.v[7 - i]);
+        vg_finish_point<VG_FMT_P2TR, MODE>(P, dv, dg, first + (unsigned long long)k, ((ok_mask >> k) & 1u) != 0);
+    }
+}
