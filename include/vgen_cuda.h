@@ -132,6 +132,21 @@ int vgen_pattern_dfa(int format, const char *pattern, int case_insensitive, uint
                      uint8_t *accept, size_t accept_cap, uint8_t sym_class[64], uint32_t info[4]);
 int vgen_pattern_lowering(int format, const char *pattern, int case_insensitive, char *out, size_t cap);
 
+
+/* ---- CLI support (host only): the reference's pattern lint and difficulty heuristic
+ * (Pattern::validate_charset, src/pattern.rs:48-175; Pattern::estimate_difficulty, src/pattern.rs:177-253), its provider
+ * lookup (provider::resolve / build_pattern / build_exact_pattern, src/provider.rs:12-63; only an embedded subset of
+ * boha's b1000 collection) and the key parser of `verify` (src/lib.rs:387-401). */
+int vgen_pattern_validate_charset(int format, const char *pattern, int case_insensitive, char *invalid_chars_out, size_t cap);
+uint64_t vgen_pattern_estimate_difficulty(int format, const char *pattern, int case_insensitive);
+/* 1 = resolved (address, format, key range filled), 0 = not a provider reference, <0 = provider error (message in err) */
+int vgen_provider_resolve(const char *ref, char *address, size_t cap, int *format, uint8_t start_be[32], uint8_t end_be[32],
+                          int *has_range, char *err, size_t err_cap);
+/* "^<escaped prefix>" for prefix_len > 0, "^<escaped address>$" for prefix_len <= 0 */
+int vgen_provider_pattern(const char *address, int prefix_len, char *out, size_t cap);
+/* WIF or hex -> 32-byte key; VGEN_ERR_INVALID_ARG if neither, VGEN_ERR_RANGE if the scalar is 0 or >= n */
+int vgen_parse_key(const char *text, uint8_t key_be[32], int *is_wif, int *compressed);
+
 #ifdef __cplusplus
 }
 #endif

@@ -147,3 +147,62 @@ def test_intervals_exhaustive_small_prefixes():
         for p in pats:
             if a.startswith(p[1:]):
                 assert _covered(lows[p], dg), (p, a, dg.hex())
+
+
+# ---- pattern lint / difficulty / provider (CLI support): the reference's own unit tests, src/pattern.rs:355-635 ----
+@pytest.mark.parametrize("pat,ci,fmt,want", [
+    ("^1Ab", False, "p2pkh", 58 ** 2), ("^1Ab", True, "p2pkh", 34 ** 2), ("^bc1qab", False, "p2wpkh", 32 ** 2), ("^1", False, "p2pkh", 1),
+    ("^0xdead", False, "ethereum", 16 ** 4), ("dead$", False, "p2pkh", 58 ** 4), ("Cat", False, "p2pkh", 58 ** 3),
+    ("^Cat", False, "p2pkh", 58 ** 3), ("^bc1ab", False, "p2wpkh", 32 ** 2), ("^bc1pab", False, "p2tr", 32 ** 2),
+    ("^1[Oo]ri", False, "p2pkh", 58 ** 2), ("^1" + "A" * 30, False, "p2pkh", 2 ** 64 - 1),      # saturating_pow
+])
+def test_estimate_difficulty_reference_cases(pat, ci, fmt, want):
+    assert vg.Pattern(pat, ci).estimate_difficulty(vg.AddressFormat.parse(fmt)) == want
+
+
+@pytest.mark.parametrize("pat,fmt,want", [
+    ("^1OR", "p2pkh", ["O"]), ("^1Cat", "p2pkh", []), ("^10ri", "p2pkh", ["0"]), ("^1OIl0", "p2pkh", ["O", "I", "l", "0"]),
+    ("^bc1qAB", "p2wpkh", ["b", "1", "A", "B"]), ("^0xghi", "ethereum", ["g", "h", "i"]), ("^1[0OIl]", "p2pkh", ["0", "O", "I", "l"]),
+    ("^1[Aa]", "p2pkh", []), ("^1[a-z]", "p2pkh", []), ("^1[A0]", "p2pkh", []), ("^1[^0]", "p2pkh", []), ("^1[0-9a]", "p2pkh", []),
+    ("^1[I-O]", "p2pkh", []), ("^1[0]", "p2pkh", ["0"]), ("^1[-A]", "p2pkh", []), ("^1[A-]", "p2pkh", []), ("^1[-0]", "p2pkh", ["0"]),
+    ("^1[.]", "p2pkh", ["."]), ("^1[_]", "p2pkh", ["_"]), ("^1[.A]", "p2pkh", []), ("^1[\\.]", "p2pkh", ["."]), ("^1[\\^^]", "p2pkh", ["^"]),
+])
+def test_validate_charset_reference_cases(pat, fmt, want):
+    assert vg.Pattern(pat).validate_charset(vg.AddressFormat.parse(fmt)) == want
+
+
+def test_provider_shim():
+    """src/provider.rs:12-63,76-87: boha:b1000:1 is the address of key 1; ranges are 2^(N-1)..2^N-1; every embedded
+    solved entry is re-derived from its published key by the oracle."""
+    import oracle
+    from vgen_b200 import provider
+    assert provider.resolve("^1Cat") is None and provider.resolve("foo:bar") is None
+    r = provider.resolve("boha:b1000:1")
+    assert r.address == "1BgGZ9tcN4rm9KBzDn7KprQz87SZ26SAMH" and r.format == vg.AddressFormat.P2pkh and r.key_range == (1, 1)
+    r66 = provider.resolve("boha:b1000:66")
+    assert r66.address == "13zb1hQbWVsc2S7ZTZnP2G4undNNpdh5so" and r66.key_range == (2 ** 65, 2 ** 66 - 1)      # README.md:107-108
+    assert provider.build_pattern(r66, 5) == "^13zb1" and provider.build_exact_pattern(r66) == "^13zb1hQbWVsc2S7ZTZnP2G4undNNpdh5so$"
+    assert provider.build_pattern(r66, 999) == "^13zb1hQbWVsc2S7ZTZnP2G4undNNpdh5so"
+    solved = {1: 1, 2: 3, 3: 7, 4: 8, 5: 0x15, 6: 0x31, 7: 0x4c, 8: 0xe0, 9: 0x1d3, 10: 0x202, 11: 0x483, 12: 0xa7b, 13: 0x1460, 14: 0x2930,
+              15: 0x68f3, 16: 0xc936, 17: 0x1764f, 18: 0x3080d, 19: 0x5749f, 20: 0xd2c55}
+    for n, k in solved.items():
+        r = provider.resolve("boha:b1000:%d" % n)
+        assert r.key_range[0] <= k <= r.key_range[1] and oracle.address("p2pkh", k)[0] == r.address
+    for bad in ("boha:b1000:67", "boha:b1000:x", "boha:other:1"):
+        with pytest.raises(ValueError):
+            provider.resolve(bad)
+
+
+def test_parse_key():
+    import ctypes as C
+    from vgen_b200 import _cabi
+    L = _cabi.lib()
+    key, w, c = C.create_string_buffer(32), C.c_int(0), C.c_int(0)
+    # README.md:121-127: WIF 5HueCGU8... <-> hex 0c28fca3...
+    assert L.vgen_parse_key(b"5HueCGU8rMjxEXxiPuD5BDku4MkFqeZyd4dZ1jvhTVqvbTLvyTJ", key, C.byref(w), C.byref(c)) == 0
+    assert key.raw.hex() == "0c28fca386c7a227600b2fe50b7cae11ec86d3bf1fbe471be89827e19d72aa1d" and w.value == 1 and c.value == 0
+    assert L.vgen_parse_key(b"KwDiBf89QgGbjEhKnhXJuH7LrciVrZi3qYjgd9M7rFU73sVHnoWn", key, C.byref(w), C.byref(c)) == 0
+    assert int.from_bytes(key.raw, "big") == 1 and c.value == 1
+    assert L.vgen_parse_key(b"0x" + b"00" * 31 + b"02", key, C.byref(w), C.byref(c)) == 0 and w.value == 0 and key.raw[-1] == 2
+    assert L.vgen_parse_key(b"00" * 32, key, None, None) < 0 and L.vgen_parse_key(b"zz", key, None, None) < 0
+    assert L.vgen_parse_key(b"ff" * 32, key, None, None) < 0

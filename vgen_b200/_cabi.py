@@ -48,6 +48,11 @@ SYMBOLS = {
     "vgen_plan_windows": (C.c_int64, [C.c_char_p, C.c_char_p, C.c_int, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_uint64]),
     "vgen_pattern_dfa": (C.c_int, [C.c_int, C.c_char_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.POINTER(C.c_uint32)]),
     "vgen_pattern_lowering": (C.c_int, [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]),
+    "vgen_pattern_validate_charset": (C.c_int, [C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]),
+    "vgen_pattern_estimate_difficulty": (C.c_uint64, [C.c_int, C.c_char_p, C.c_int]),
+    "vgen_provider_resolve": (C.c_int, [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_int), C.c_char_p, C.c_char_p, C.POINTER(C.c_int), C.c_char_p, C.c_size_t]),
+    "vgen_provider_pattern": (C.c_int, [C.c_char_p, C.c_int, C.c_char_p, C.c_size_t]),
+    "vgen_parse_key": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
 }
 
 _lib = None

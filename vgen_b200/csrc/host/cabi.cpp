@@ -1,6 +1,7 @@
 // extern "C" surface of libvgen_cuda.so (include/vgen_cuda.h) over vg::Engine.
 #include "../../../include/vgen_cuda.h"
 #include "engine.h"
+#include "pattern_lint.h"
 #include <string.h>
 #include <stdio.h>
 #include <new>
@@ -265,6 +266,61 @@ int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, si
         for (int i = 0; i < lp.dev.exact_words * 4; i++) { snprintf(buf, sizeof buf, "%02x", (lp.dev.exact[i / 4] >> (8 * (i % 4))) & 0xff); s += buf; }
     }
     return copy_out(s, out, cap);
+}
+
+// ---- CLI support: lint, difficulty, provider, key parsing (host only) ----
+int vgen_pattern_validate_charset(int format, const char *pattern, int ci, char *out, size_t cap) {
+    if (!pattern || format < 0 || format > 5) return VGEN_ERR_INVALID_ARG;
+    return copy_out(vg::validate_charset(pattern, ci != 0, format), out, cap);
+}
+uint64_t vgen_pattern_estimate_difficulty(int format, const char *pattern, int ci) {
+    if (!pattern || format < 0 || format > 5) return 0;
+    return vg::estimate_difficulty(pattern, ci != 0, format);
+}
+int vgen_provider_resolve(const char *ref, char *address, size_t cap, int *format, uint8_t start_be[32], uint8_t end_be[32],
+                          int *has_range, char *errbuf, size_t err_cap) {
+    if (!ref || !address || !format || !start_be || !end_be || !has_range) return VGEN_ERR_INVALID_ARG;
+    vg::ProviderResult r; std::string err;
+    int rc = vg::provider_resolve(ref, r, err);
+    if (rc < 0) { if (errbuf && err_cap) { strncpy(errbuf, err.c_str(), err_cap - 1); errbuf[err_cap - 1] = 0; } return VGEN_ERR_PATTERN; }
+    if (rc == 0) return 0;
+    if (copy_out(r.address, address, cap) < 0) return VGEN_ERR_BUFFER;
+    *format = r.format; *has_range = r.has_range ? 1 : 0;
+    r.start.to_be(start_be); r.end.to_be(end_be);
+    return 1;
+}
+int vgen_provider_pattern(const char *address, int prefix_len, char *out, size_t cap) {
+    if (!address) return VGEN_ERR_INVALID_ARG;
+    vg::ProviderResult r; r.address = address;
+    return copy_out(prefix_len > 0 ? vg::provider_build_pattern(r, (size_t)prefix_len) : vg::provider_build_exact_pattern(r), out, cap);
+}
+// WIF (mainnet, compressed or not) or 64 hex digits (optional 0x) -> key; the `verify` command's parser (src/lib.rs:387-401)
+int vgen_parse_key(const char *text, uint8_t key_be[32], int *is_wif, int *compressed) {
+    if (!text || !key_be) return VGEN_ERR_INVALID_ARG;
+    std::string s = text;
+    std::vector<uint8_t> payload;
+    if (vg::h_base58check_decode(s, payload) && (payload.size() == 33 || (payload.size() == 34 && payload[33] == 0x01)) && payload[0] == 0x80) {
+        memcpy(key_be, payload.data() + 1, 32);
+        if (is_wif) *is_wif = 1;
+        if (compressed) *compressed = payload.size() == 34;
+    } else {
+        while (s.size() >= 2 && s[0] == '0' && s[1] == 'x') s = s.substr(2);           // trim_start_matches("0x")
+        if (s.size() != 64) return VGEN_ERR_INVALID_ARG;
+        for (int i = 0; i < 32; i++) {
+            int v = 0;
+            for (int j = 0; j < 2; j++) {
+                int c = s[2 * i + j], d;
+                if (c >= '0' && c <= '9') d = c - '0'; else if (c >= 'a' && c <= 'f') d = c - 'a' + 10; else if (c >= 'A' && c <= 'F') d = c - 'A' + 10; else return VGEN_ERR_INVALID_ARG;
+                v = v * 16 + d;
+            }
+            key_be[i] = (uint8_t)v;
+        }
+        if (is_wif) *is_wif = 0;
+        if (compressed) *compressed = 1;
+    }
+    vg::U256 k = vg::U256::from_be(key_be);
+    if (k.is_zero() || vg::secp_order_minus1() < k) return VGEN_ERR_RANGE;             // SecretKey::from_slice rejects 0 and >= n
+    return VGEN_OK;
 }
 
 }  // extern "C"

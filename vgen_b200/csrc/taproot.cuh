@@ -16,7 +16,7 @@
 #include "match.cuh"
 
 #ifndef VG_TAP_GROUP
-#define VG_TAP_GROUP 8          // keys handled by one stage-2 thread = keys sharing one field inversion
+#define VG_TAP_GROUP 16         // keys handled by one stage-2 thread = keys sharing one field inversion
 #endif
 
 // t as 8 big-endian words (t[0] most significant) of the TapTweak tagged hash of the x-only key
@@ -37,8 +37,27 @@ VG_DEV bool vg_tweak_is_valid(const uint32_t t[8]) {
     VG_UNROLL for (int i = 0; i < 8; i++) any |= k[i];
     return any == 0 || scalar_is_valid(k);          // t == 0 is allowed by BIP341 (Q = P)
 }
+// r = a + (bx, by) for a finite Jacobian a, generic case only (8M + 3S, no calls). Returns false when the two points share
+// their x coordinate (doubling / opposite points): the caller then redoes the key with the complete formulas.
+VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
+    fe z2, u2, s2, h, rr, h2, h3, v, t;
+    fe_sqr(z2, a.z); fe_mul(u2, bx, z2);
+    fe_mul(s2, by, z2); fe_mul(s2, s2, a.z);
+    fe_sub(h, u2, a.x); fe_sub(rr, s2, a.y);
+    fe hc = h; fe_canon(hc);
+    if (fe_is_zero_raw(hc)) return false;
+    fe_sqr(h2, h); fe_mul(h3, h2, h); fe_mul(v, a.x, h2);
+    fe_sqr(t, rr); fe_sub(t, t, h3); fe_sub(t, t, v); fe_sub(t, t, v);      // X3
+    fe_sub(v, v, t); fe_mul(v, rr, v); fe_mul(h3, a.y, h3); fe_sub(a.y, v, h3);
+    a.x = t;
+    fe_mul(a.z, a.z, h);
+    return true;
+}
+
 // Q = P + t*G in Jacobian coordinates. Returns false when Q is the point at infinity (t*G = -P).
-// gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
+// FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false).
+// FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
+template <bool FAST>
 VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
     const uint32_t n_win = 256u / bits, mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
@@ -62,11 +81,14 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
         bx.v[0] = a0.x; bx.v[1] = a0.y; bx.v[2] = a0.z; bx.v[3] = a0.w; bx.v[4] = a1.x; bx.v[5] = a1.y; bx.v[6] = a1.z; bx.v[7] = a1.w;
         by.v[0] = a2.x; by.v[1] = a2.y; by.v[2] = a2.z; by.v[3] = a2.w; by.v[4] = a3.x; by.v[5] = a3.y; by.v[6] = a3.z; by.v[7] = a3.w;
 #endif
-        gej_t r;
-        gej_add_affine(r, q, bx, by);
-        q = r;
+        if (FAST) { if (!vg_gej_add_affine_fast(q, bx, by)) return false; }
+        else { gej_t r; gej_add_affine(r, q, bx, by); q = r; if (q.inf) { fe_set_one(q.z); } }
     }
     return !q.inf;
+}
+
+VG_COLD bool vg_tap_output_key_slow(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
+    return vg_tap_output_key<false>(q, px, py, t, tab, bits);
 }
 
 // stage-2 thread: keys [first, first + VG_TAP_GROUP) of the window
@@ -98,7 +120,8 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
             vg_taptweak_hash(t, px);
             ok = vg_tweak_is_valid(t);
             gej_t q;
-            if (ok) ok = vg_tap_output_key(q, px, py, t, P.tap_table, P.tap_bits);
+            if (ok && !vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits))
+                ok = vg_tap_output_key_slow(q, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
             if (ok) { X[k] = q.x; fe_sqr(z2, q.z); }
         }
         if (ok) ok_mask |= 1u << k;

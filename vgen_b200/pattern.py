@@ -29,6 +29,16 @@ class Pattern:
     def is_case_insensitive(self):
         return self._ci
 
+    def validate_charset(self, fmt):                                          # src/pattern.rs:48-175
+        buf = C.create_string_buffer(512)
+        n = _cabi.lib().vgen_pattern_validate_charset(int(fmt), self._pattern.encode(), int(self._ci), buf, 512)
+        if n < 0:
+            raise _cabi.VgenError(n, "vgen_pattern_validate_charset")
+        return list(buf.value.decode())
+
+    def estimate_difficulty(self, fmt):                                       # src/pattern.rs:177-253
+        return int(_cabi.lib().vgen_pattern_estimate_difficulty(int(fmt), self._pattern.encode(), int(self._ci)))
+
     def lowering(self, fmt):
         """How the scan path will test this pattern on the device for `fmt`: dict(kind=..., intervals=[(lo, hi), ...])."""
         buf = C.create_string_buffer(4096)
