@@ -22,7 +22,7 @@ P_FIELD = 2**256 - 2**32 - 977
 @pytest.fixture(scope="module")
 def emu():
     csrc = os.path.join(HERE, "..", "vgen_b200", "csrc")
-    deps = [SRC] + [os.path.join(csrc, f) for f in ("fe.cuh", "ec.cuh", "hash.cuh", "scan_core.cuh", "match.cuh", "encode.cuh", "scan_types.h")]
+    deps = [SRC] + [os.path.join(csrc, f) for f in ("fe.cuh", "ec.cuh", "hash.cuh", "scan_core.cuh", "match.cuh", "taproot.cuh", "scan_types.h")]
     deps = [d for d in deps if os.path.exists(d)]
     if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", "-fPIC", "-shared", "-o", LIB, SRC])
@@ -120,7 +120,7 @@ def test_p2tr_two_stage_vs_oracle(emu):
 
 def test_p2tr_stage2_invalid_points_and_small_tweak_table(emu):
     # all-zero points (invalid scalar / outside the range) give all-zero programs; 8-bit windows agree with 4-bit ones
-    ks = [1, 2, 3, 0, 2**200 + 9, N - 1, 0, 77]
+    ks = [1, 2, 3, 0, 2**200 + 9, N - 1, 0, 77, 5, 0, 0, 2**255, 12345, N - 2, 0, 9]      # a multiple of VG_TAP_GROUP (16)
     pts = (C.c_uint32 * (16 * len(ks)))()
     for i, k in enumerate(ks):
         if k:

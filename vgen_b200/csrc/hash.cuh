@@ -288,7 +288,15 @@ VG_CONST uint64_t VG_KECCAK_RC[24] = {
 
 VG_DEV uint64_t vg_rotl64(uint64_t x, int n) { return (x << n) | (x >> (64 - n)); }
 
+// VG_KECCAK_UNROLL: 1 = fully unrolled rounds (round-constant loads fold, the zero lanes of the first round and the
+// unused lanes of the last one are eliminated), 0 = rolled loop (smaller code)
+#ifndef VG_KECCAK_UNROLL
+#define VG_KECCAK_UNROLL 0
+#endif
 VG_DEV void keccak_f1600(uint64_t s[25]) {
+#if VG_KECCAK_UNROLL && !defined(VG_HOST_EMU)
+    #pragma unroll
+#endif
     for (int r = 0; r < 24; r++) {
         uint64_t c0 = s[0] ^ s[5] ^ s[10] ^ s[15] ^ s[20], c1 = s[1] ^ s[6] ^ s[11] ^ s[16] ^ s[21];
         uint64_t c2 = s[2] ^ s[7] ^ s[12] ^ s[17] ^ s[22], c3 = s[3] ^ s[8] ^ s[13] ^ s[18] ^ s[23];

@@ -325,27 +325,33 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         }
         const U256 base = S.base;
         const bool with_text = n_hits <= kEagerTextHits;
-        auto job = [this, recs, base, li, fmt, with_text]() {
-            std::vector<Hit> out;
-            out.reserve(recs->size());
-            for (const vg_hit_rec &R : *recs) {
-                Hit h; memset(h.digest, 0, 32);
-                h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = li;
-                for (int w = 0; w < 8; w++) for (int b = 0; b < 4; b++) h.digest[4 * w + b] = (uint8_t)(R.digest[w] >> (8 * b));
-                // exact confirmation on the host: re-encode the address from the digest and run the full DFA
-                std::string addr = format_address(fmt, h.digest);
-                if (!lp_.dfa.match(addr.data(), addr.size())) continue;
-                h.key = base.add64(((uint64_t)R.idx_hi << 32) | R.idx_lo);
-                if (with_text) {
-                    uint8_t kb[32]; h.key.to_be(kb);
-                    h.text = h_hex(kb, 32) + " " + addr + " " + format_wif(fmt, kb) + "\n";
+        // big windows are confirmed in up to 4 slices so that the last window's job is not a serial tail
+        const size_t n_rec = recs->size();
+        const size_t n_slices = n_rec >= 256 ? 4 : 1;
+        for (size_t sl = 0; sl < n_slices; sl++) {
+            const size_t lo = n_rec * sl / n_slices, hi = n_rec * (sl + 1) / n_slices;
+            auto job = [this, recs, base, li, fmt, with_text, lo, hi]() {
+                std::vector<Hit> out;
+                out.reserve(hi - lo);
+                for (size_t r = lo; r < hi; r++) {
+                    const vg_hit_rec &R = (*recs)[r];
+                    Hit h; memset(h.digest, 0, 32);
+                    h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = li;
+                    for (int w = 0; w < 8; w++) for (int b = 0; b < 4; b++) h.digest[4 * w + b] = (uint8_t)(R.digest[w] >> (8 * b));
+                    // exact confirmation on the host: re-encode the address from the digest and run the full DFA
+                    std::string addr = format_address(fmt, h.digest);
+                    if (!lp_.dfa.match(addr.data(), addr.size())) continue;
+                    h.key = base.add64(((uint64_t)R.idx_hi << 32) | R.idx_lo);
+                    if (with_text) {
+                        uint8_t kb[32]; h.key.to_be(kb);
+                        h.text = h_hex(kb, 32) + " " + addr + " " + format_wif(fmt, kb) + "\n";
+                    }
+                    out.push_back(std::move(h));
                 }
-                out.push_back(std::move(h));
-            }
-            std::sort(out.begin(), out.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
-            return out;
-        };
-        pending.push_back(std::async(recs->size() >= 64 ? std::launch::async : std::launch::deferred, job));
+                return out;
+            };
+            pending.push_back(std::async(n_rec >= 64 ? std::launch::async : std::launch::deferred, job));
+        }
         if (max_hits) drain(false);                       // a hit limit needs the confirmed count now
         else drain(true);                                  // otherwise only reap the jobs that are already finished
         keys_scanned += S.limit;

@@ -10,7 +10,7 @@ import time
 from . import _cabi
 from .address import AddressFormat, GeneratedAddress, address_from_digest, wif_from_key
 from .pattern import Pattern
-from .scanner import ScanConfig, ScanResult
+from .scanner import MatchList, ScanConfig, ScanResult
 
 DEFAULT_BATCH_SIZE = 512 * 1024          # src/gpu.rs:83; here only a keys-per-launch hint (0 = fill the GPU)
 SECP256K1_N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
@@ -141,6 +141,20 @@ class GpuRunner:
             out += conv(hits, n)
         return out, scanned.value
 
+    def fetch_text(self, total):
+        """bytes: "<key hex> <address> <wif>\\n" for every hit of the last scan (vgen_cuda_scan_fetch_text), copied out of the library."""
+        chunks, got = [], 0
+        cap = 1 << 22
+        buf = C.create_string_buffer(cap)
+        n = C.c_uint64(0)
+        while got < total:
+            nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, got, total - got, buf, cap, C.byref(n)))
+            if nb <= 0 or n.value == 0:
+                break
+            chunks.append(C.string_at(buf, nb))
+            got += n.value
+        return b"".join(chunks), got
+
     def fetch_records(self, total):
         """(key_hex[], address[], wif[]) of every hit of the last scan, formatted by the library (vgen_cuda_scan_fetch_text)."""
         toks, got = [], 0
@@ -213,8 +227,8 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
                                  hits_cap=1, fetch_all=False)
     total = int(runner._lib.vgen_cuda_scan_total_hits(runner._ctx))
     elapsed = time.perf_counter() - t0
-    keys, addrs, wifs = runner.fetch_records(total)
-    matches = list(map(GeneratedAddress, addrs, wifs, keys, itertools.repeat(fmt)))
+    text, got = runner.fetch_text(total)
+    matches = MatchList(text, got, fmt)
     elapsed = time.perf_counter() - t0
     return ScanResult(matches=matches, operations=scanned, elapsed_secs=elapsed)
 
