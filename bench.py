@@ -24,7 +24,9 @@ METRIC = "Mkeys/s P2PKH ^1Cat scan"
 START = 1 << 64
 # algorithmic work per key, 32-bit integer instruction slots (DESIGN.md "Roofline"; SURVEY.md 8d, +/- variant, c_w = 1):
 #   EC 3.5M + 1S = 300.5 limb products + ~300 carry/add slots, SHA-256 ~1400, RIPEMD-160 ~975, matcher ~15
-W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed": 4450, "ethereum": 5220}
+W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed": 4450, "ethereum": 5220,
+         # P2TR: walk 4.5 field mults + tweak stage 16 x (8M + 3S) + 4 + 270/16 = ~201.5 mults x ~147 slots, + one SHA-256 compression
+         "p2tr": 31000}
 HBM_BYTES_PER_KEY = 32          # prefix-product scratch: 32 B written + 32 B read per +/- key pair
 
 
@@ -222,7 +224,7 @@ def run_own(args):
     e2e = {"value": e_total / (e_ms * 1e-3) / 1e6, "unit": "Mkeys/s",
            "h2d_bytes_per_step": (io1[0] - io0[0]) // K, "d2h_bytes_per_step": (io1[1] - io0[1]) // K,
            "ms_per_step": e_ms / K, "hits_per_step": e_hits_total / K,
-           "api": "vgen_b200.scan_gpu_with_runner -> vgen_cuda_scan (host scalars in, confirmed hit records out)"}
+           "api": "vgen_b200.scan_gpu_with_runner -> vgen_cuda_scan + vgen_cuda_scan_fetch_text (host scalars in; confirmed hits formatted as key/address/WIF text and copied to the caller; Python objects are built lazily on access)"}
 
     # ---- roofline of the walk kernel (the only kernel in the timed region): integer issue, not HBM / tensor
     peaks = load_json(os.path.join(ROOT, "MEASURED_PEAKS.json")) or {}
