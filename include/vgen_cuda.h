@@ -105,6 +105,9 @@ int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t
 /* kernel launches issued by this context so far; keys per full-size window */
 uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx);
 uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx);
+/* lanes of the context: every GPU is driven through 2 streams (each with its own centres, scratch and hit buffers) whose
+ * windows overlap, so that a window's late warps do not leave the SMs under-occupied; lanes = 2 x GPUs */
+int vgen_cuda_lane_count(const vgen_ctx *ctx);
 /* bytes the scans of this context copied host->device (start scalars, launch parameters) and device->host (counters, hit records) */
 void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h);
 

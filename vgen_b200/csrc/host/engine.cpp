@@ -11,6 +11,7 @@
 #include <deque>
 #include <future>
 #include <string.h>
+#include <stdlib.h>
 
 namespace vg {
 
@@ -20,6 +21,12 @@ static const int kCounterWords = 4;
 static const uint32_t kEagerTextHits = 1u << 16;   // windows with at most this many device hits get their text records built by the confirm job
 
 Engine::~Engine() { destroy(); }
+
+int Engine::lanes_per_device() {
+    const char *e = getenv("VGEN_LANES_PER_GPU");       // tuning override
+    int n = e ? atoi(e) : 2;
+    return n < 1 ? 1 : (n > 4 ? 4 : n);
+}
 
 void Engine::destroy() {
     for (auto &L : lanes_) {
@@ -59,7 +66,10 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
         if (prop.major < 10) { err = std::string("device ") + prop.name + " is not sm_100 class; this library is built for B200 (sm_100a) only"; return false; }
         Lane L; L.device = d; L.sm_count = prop.multiProcessorCount; L.name = prop.name;
         min_sm = std::min(min_sm, L.sm_count);
-        lanes_.push_back(L);
+        // Several lanes (stream + centres + scratch + hit buffers) per GPU: a window's warps do not finish together
+        // (ncu r01: 12.9 of 16 resident warps active on average), and a second stream's next window fills the CTA slots the
+        // early finishers free. Measured on B200: 1 lane 5,819, 2 lanes 6,094, 3 lanes 6,085 Mkeys/s (profiles/overlap_r01.log).
+        for (int k = 0; k < lanes_per_device(); k++) lanes_.push_back(L);
     }
     levels_ = compute_levels(min_sm, hint, half_, VG_BLOCK, VG_CTAS_PER_SM);
     const Level &F = levels_.back();
@@ -330,13 +340,14 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         const size_t n_slices = n_rec >= 256 ? 4 : 1;
         for (size_t sl = 0; sl < n_slices; sl++) {
             const size_t lo = n_rec * sl / n_slices, hi = n_rec * (sl + 1) / n_slices;
-            auto job = [this, recs, base, li, fmt, with_text, lo, hi]() {
+            const uint32_t dev_index = (uint32_t)L.device;
+            auto job = [this, recs, base, dev_index, fmt, with_text, lo, hi]() {
                 std::vector<Hit> out;
                 out.reserve(hi - lo);
                 for (size_t r = lo; r < hi; r++) {
                     const vg_hit_rec &R = (*recs)[r];
                     Hit h; memset(h.digest, 0, 32);
-                    h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = li;
+                    h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = dev_index;
                     for (int w = 0; w < 8; w++) for (int b = 0; b < 4; b++) h.digest[4 * w + b] = (uint8_t)(R.digest[w] >> (8 * b));
                     // exact confirmation on the host: re-encode the address from the digest and run the full DFA
                     std::string addr = format_address(fmt, h.digest);
@@ -445,31 +456,45 @@ bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *ou
 bool Engine::bench_resident(const U256 &start, uint32_t n_windows, float &ms, uint64_t &keys, uint64_t &nlaunch, std::string &err) {
     if (!has_pattern_) { err = "no pattern set"; return false; }
     if (!compute_stride_points(err)) return false;
-    Lane &L = lanes_[0];
-    CK(cudaSetDevice(L.device));
+    // the lanes of the first device, exactly as a scan drives them: window k of the sequence goes to lane k mod G
+    std::vector<Lane *> ls;
+    for (auto &L : lanes_) if (L.device == lanes_[0].device) ls.push_back(&L);
+    const uint32_t nl = (uint32_t)ls.size();
+    CK(cudaSetDevice(ls[0]->device));
     const int fl = (int)levels_.size() - 1;
-    uint64_t gl = (uint64_t)shard_index_ * lanes_.size();
-    U256 base = start.add(U256(gl).mul64(levels_[fl].window));
-    if (!setup_centers(L, fl, base, err)) return false;
-    Slot &S = L.slot[0];
-    S.base = base; S.level = fl; S.limit = levels_[fl].window;
-    vg_scan_params P; fill_params(L, S, P);
-    cudaEvent_t e0, e1;
-    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-    CK(cudaStreamSynchronize(L.stream));
-    CK(cudaEventRecord(e0, L.stream));
-    for (uint32_t w = 0; w < n_windows; w++) {
-        CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
-        CK(launch_walk(lp_.format, VG_MODE_MATCH, P, levels_[fl].blocks, L.stream));
-        if (lp_.format == VG_FMT_P2TR) { CK(launch_taptweak(VG_MODE_MATCH, P, L.stream)); launches++; }
+    const uint64_t W = levels_[fl].window;
+    std::vector<vg_scan_params> Ps(nl);
+    for (uint32_t j = 0; j < nl; j++) {
+        Lane &L = *ls[j];
+        uint64_t gl = (uint64_t)shard_index_ * lanes_.size() + j;
+        U256 base = start.add(U256(gl).mul64(W));
+        if (!setup_centers(L, fl, base, err)) return false;
+        Slot &S = L.slot[0];
+        S.base = base; S.level = fl; S.limit = W;
+        fill_params(L, S, Ps[j]);
+        CK(cudaStreamSynchronize(L.stream));
     }
-    CK(cudaEventRecord(e1, L.stream));
+    cudaEvent_t e0, e1; std::vector<cudaEvent_t> done(nl);
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    for (auto &d : done) CK(cudaEventCreateWithFlags(&d, cudaEventDisableTiming));
+    cudaStream_t s0 = ls[0]->stream;
+    CK(cudaEventRecord(e0, s0));
+    for (uint32_t j = 1; j < nl; j++) CK(cudaStreamWaitEvent(ls[j]->stream, e0, 0));      // no lane starts before e0
+    for (uint32_t w = 0; w < n_windows; w++) {
+        Lane &L = *ls[w % nl]; Slot &S = L.slot[0];
+        CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
+        CK(launch_walk(lp_.format, VG_MODE_MATCH, Ps[w % nl], levels_[fl].blocks, L.stream));
+        if (lp_.format == VG_FMT_P2TR) { CK(launch_taptweak(VG_MODE_MATCH, Ps[w % nl], L.stream)); launches++; }
+    }
+    for (uint32_t j = 1; j < nl; j++) { CK(cudaEventRecord(done[j], ls[j]->stream)); CK(cudaStreamWaitEvent(s0, done[j], 0)); }
+    CK(cudaEventRecord(e1, s0));                                                           // after every lane's last window
     CK(cudaEventSynchronize(e1));
     CK(cudaEventElapsedTime(&ms, e0, e1));
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    for (auto &d : done) cudaEventDestroy(d);
     launches += n_windows; nlaunch = n_windows;
-    keys = (uint64_t)n_windows * levels_[fl].window;
-    L.centers_level = -1;
+    keys = (uint64_t)n_windows * W;
+    for (auto *L : ls) L->centers_level = -1;
     return true;
 }
 

@@ -63,6 +63,7 @@ public:
     bool bench_resident(const U256 &start, uint32_t n_windows, float &ms, uint64_t &keys, uint64_t &launches, std::string &err);
     const LoweredPattern &pattern() const { return lp_; }
     bool has_pattern() const { return has_pattern_; }
+    static int lanes_per_device();      // lanes (streams) the engine opens on every GPU (default 2, VGEN_LANES_PER_GPU)
     int n_lanes() const { return (int)lanes_.size(); }
     const Lane &lane(int i) const { return lanes_[i]; }
     uint32_t half() const { return half_; }

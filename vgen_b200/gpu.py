@@ -107,6 +107,9 @@ class GpuRunner:
     def matcher_kind(self):
         return self._lib.vgen_cuda_matcher_kind(self._ctx).decode()
 
+    def lane_count(self):
+        return int(self._lib.vgen_cuda_lane_count(self._ctx))
+
     def launch_count(self):
         return int(self._lib.vgen_cuda_launch_count(self._ctx))
 
