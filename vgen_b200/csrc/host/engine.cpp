@@ -41,7 +41,7 @@ void Engine::destroy() {
             if (S.done) cudaEventDestroy(S.done);
         }
         for (void *p : {(void *)L.d_pow2, (void *)L.d_gtab, (void *)L.d_centers, (void *)L.d_scratch, (void *)L.d_base8,
-                        (void *)L.d_stride_pts, (void *)L.d_points, (void *)L.d_tap_table, (void *)L.d_dfa_table, (void *)L.d_dfa_accept})
+                        (void *)L.d_stride_pts, (void *)L.d_points, (void *)(L.owns_tap_table ? L.d_tap_table : nullptr), (void *)L.d_dfa_table, (void *)L.d_dfa_accept})
             if (p) cudaFree(p);
         if (L.h_hits) cudaFreeHost(L.h_hits);
         if (L.own_stream && L.stream) cudaStreamDestroy(L.stream);
@@ -140,7 +140,10 @@ bool Engine::ensure_taproot(std::string &err) {
         if (L.d_tap_table) continue;
         CK(cudaSetDevice(L.device));
         CK(cudaMalloc(&L.d_points, (size_t)F.window * 64));
+        for (auto &O : lanes_) if (&O != &L && O.device == L.device && O.d_tap_table) L.d_tap_table = O.d_tap_table;   // one table per GPU
+        if (L.d_tap_table) continue;
         CK(cudaMalloc(&L.d_tap_table, ((size_t)(256 / kTapBits) << kTapBits) * 64));
+        L.owns_tap_table = true;
         CK(launch_build_tap_table(L.d_tap_table, kTapBits, L.d_pow2, L.stream));
         launches++;
         CK(cudaStreamSynchronize(L.stream));

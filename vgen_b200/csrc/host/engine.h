@@ -35,6 +35,7 @@ struct Lane {
     bool own_stream = true;
     int sm_count = 0;
     uint32_t *d_pow2 = nullptr, *d_gtab = nullptr, *d_centers = nullptr, *d_scratch = nullptr, *d_base8 = nullptr;
+    bool owns_tap_table = false;                 // the lanes of one GPU share the table
     uint32_t *d_points = nullptr, *d_tap_table = nullptr;   // P2TR only, allocated on first use (taproot.cuh)
     uint32_t *d_stride_pts = nullptr;          // [n_levels][16] scratch for stride points
     uint16_t *d_dfa_table = nullptr; uint8_t *d_dfa_accept = nullptr;
