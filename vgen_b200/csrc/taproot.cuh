@@ -15,6 +15,9 @@
 #pragma once
 #include "match.cuh"
 
+#ifndef VG_TAP_SYNC
+#define VG_TAP_SYNC 1
+#endif
 #ifndef VG_TAP_GROUP
 #define VG_TAP_GROUP 16         // keys handled by one stage-2 thread = keys sharing one field inversion
 #endif
@@ -102,6 +105,9 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
     #pragma unroll 1
 #endif
     for (int k = 0; k < VG_TAP_GROUP; k++) {
+#if VG_TAP_SYNC && !defined(VG_HOST_EMU)
+        __syncthreads();      // re-align the CTA's warps once per key (instruction-fetch sharing, see VG_SYNC_ITER in scan_core.cuh)
+#endif
         const uint32_t *p = P.points + (first + (unsigned long long)k) * 16;
         fe px, py;
 #ifdef VG_HOST_EMU
