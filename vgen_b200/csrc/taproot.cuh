@@ -61,19 +61,23 @@ VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
 // FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false).
 // FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
 template <bool FAST>
-VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
+VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true) {
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
+    bool special = false;
     const uint32_t n_win = 256u / bits, mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
 #ifndef VG_HOST_EMU
     #pragma unroll 1
 #endif
     for (uint32_t j = 0; j < n_win; j++) {
+#if VG_TAP_SYNC >= 2 && !defined(VG_HOST_EMU)
+        if (FAST) __syncthreads();      // every thread of the CTA runs all n_win iterations (inactive ones skip the addition)
+#endif
         const uint32_t bit = j * bits;
         // bit position counted from the least significant end of t; word 7 is the least significant
         uint32_t word = 0;
         VG_UNROLL for (int i = 0; i < 8; i++) word = ((bit >> 5) == (uint32_t)i) ? t[7 - i] : word;
         const uint32_t v = (word >> (bit & 31u)) & mask;
-        if (v == 0) continue;
+        if (v == 0 || !active || special) continue;
         const uint32_t *e = tab + ((size_t)j * ((size_t)mask + 1) + v) * 16;
         fe bx, by;
 #ifdef VG_HOST_EMU
@@ -84,10 +88,10 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
         bx.v[0] = a0.x; bx.v[1] = a0.y; bx.v[2] = a0.z; bx.v[3] = a0.w; bx.v[4] = a1.x; bx.v[5] = a1.y; bx.v[6] = a1.z; bx.v[7] = a1.w;
         by.v[0] = a2.x; by.v[1] = a2.y; by.v[2] = a2.z; by.v[3] = a2.w; by.v[4] = a3.x; by.v[5] = a3.y; by.v[6] = a3.z; by.v[7] = a3.w;
 #endif
-        if (FAST) { if (!vg_gej_add_affine_fast(q, bx, by)) return false; }
+        if (FAST) { if (!vg_gej_add_affine_fast(q, bx, by)) special = true; }
         else { gej_t r; gej_add_affine(r, q, bx, by); q = r; if (q.inf) { fe_set_one(q.z); } }
     }
-    return !q.inf;
+    return !q.inf && !special;
 }
 
 VG_COLD bool vg_tap_output_key_slow(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
@@ -105,7 +109,7 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
     #pragma unroll 1
 #endif
     for (int k = 0; k < VG_TAP_GROUP; k++) {
-#if VG_TAP_SYNC && !defined(VG_HOST_EMU)
+#if VG_TAP_SYNC == 1 && !defined(VG_HOST_EMU)
         __syncthreads();      // re-align the CTA's warps once per key (instruction-fetch sharing, see VG_SYNC_ITER in scan_core.cuh)
 #endif
         const uint32_t *p = P.points + (first + (unsigned long long)k) * 16;
@@ -121,12 +125,13 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
         bool ok = !(fe_is_zero_raw(px) && fe_is_zero_raw(py));
         fe z2; fe_set_one(z2);
         fe_set_zero(X[k]);
-        if (ok) {
+        {
             uint32_t t[8];
             vg_taptweak_hash(t, px);
-            ok = vg_tweak_is_valid(t);
+            ok = ok && vg_tweak_is_valid(t);
             gej_t q;
-            if (ok && !vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits))
+            // all threads walk the table loop together (barriers inside); invalid keys skip the additions
+            if (!vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits, ok) && ok)
                 ok = vg_tap_output_key_slow(q, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
             if (ok) { X[k] = q.x; fe_sqr(z2, q.z); }
         }
