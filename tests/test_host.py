@@ -206,3 +206,12 @@ def test_parse_key():
     assert L.vgen_parse_key(b"0x" + b"00" * 31 + b"02", key, C.byref(w), C.byref(c)) == 0 and w.value == 0 and key.raw[-1] == 2
     assert L.vgen_parse_key(b"00" * 32, key, None, None) < 0 and L.vgen_parse_key(b"zz", key, None, None) < 0
     assert L.vgen_parse_key(b"ff" * 32, key, None, None) < 0
+
+
+def test_match_list_is_a_lazy_sequence():
+    from vgen_b200.scanner import MatchList
+    text = b"00aa 1Abc Kx1\n00bb 1Def Kx2\n"
+    m = MatchList(text, 2, vg.AddressFormat.P2pkh)
+    assert len(m) == 2 and m._items is None                    # len() does not parse
+    assert m[0] == vg.GeneratedAddress("1Abc", "Kx1", "00aa", vg.AddressFormat.P2pkh) and m[-1].hex == "00bb"
+    assert [x.address for x in m] == ["1Abc", "1Def"] and m == list(m) and len(MatchList(b"", 0, vg.AddressFormat.P2pkh)) == 0
