@@ -231,3 +231,17 @@ def test_two_lanes_per_gpu_cover_the_range_once(runner):
     # every reported hit re-derived by the oracle (soundness over the full range)
     for m in res.matches[:: max(1, len(res.matches) // 200)]:
         assert oracle.address("p2pkh", int(m.hex, 16))[0] == m.address and m.address.startswith("1Ab")
+
+
+def test_dense_prefix_with_hit_limit_uses_small_windows(runner):
+    """generate -p ^1A -c 1 (src/lib.rs:347): a dense interval matcher with a hit limit starts on the ramp levels, so the
+    first match comes back after a small window instead of a full-size round of 2 x 77.6 M keys."""
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=1, start=2**64 + 5, end=None)
+    res = vg.scan_gpu_with_runner(vg.Pattern("^1A"), cfg, None, None, runner)
+    keys, _, _ = oracle.scan_range("p2pkh", "^1A", 2**64 + 5, 1 << 12)
+    assert [int(m.hex, 16) for m in res.matches] == keys[:1]
+    assert res.operations < runner.batch_size
+    # a sparse prefix with the same limit goes straight to full-size windows (no ramp): operations are whole windows
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=1, start=2**64, end=2**64 + 3 * runner.batch_size - 1)
+    res = vg.scan_gpu_with_runner(vg.Pattern("^1CatDogCat"), cfg, None, None, runner)
+    assert res.matches == [] and res.operations == 3 * runner.batch_size

@@ -256,9 +256,11 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
     if (!compute_stride_points(err)) return false;
     const uint32_t nl = (uint32_t)lanes_.size(), G = shard_count_ * nl;
     const int fl = (int)levels_.size() - 1;
-    // ramp levels only when the scan can end early: a hit limit on a matcher that may be dense (plan.h)
-    const bool sparse = lp_.dev.kind == VG_MATCH_INTERVALS || lp_.dev.kind == VG_MATCH_EXACT;
-    const WindowPlan plan(levels_, G, N, max_hits != 0 && !sparse);
+    // ramp levels (small windows first) only when the scan is likely to end early: a hit limit, and a device matcher
+    // dense enough that one full-size round would report a good part of that limit (e.g. generate -p ^1A -c 1)
+    const double per_round = lp_.density * (double)levels_.back().window * (double)G;
+    const bool ramp = max_hits != 0 && per_round > 0.25 * (double)max_hits;
+    const WindowPlan plan(levels_, G, N, ramp);
     std::vector<LaneRun> runs(nl);
     for (auto &r : runs) r.cur = plan.begin();
     uint64_t seq = 0;

@@ -200,7 +200,7 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
     for (const auto &set : info.prefix_sets) {
         std::string chars;
         for (const char *a = alpha; *a; a++) if (set[(unsigned char)*a] && chars.find(*a) == std::string::npos) chars.push_back(*a);
-        if (chars.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; return true; }   // can never match
+        if (chars.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; out.density = 0.0; return true; }   // can never match
         if (prefixes.size() * chars.size() > 64) { truncated = true; break; }
         std::vector<std::string> nx;
         for (const auto &p : prefixes) for (char c : chars) nx.push_back(p + c);
@@ -210,8 +210,8 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
 
     if (!truncated && info.rest_is_end && prefixes.size() == 1) {
         uint8_t dg[32];
-        if (!decode_exact(format, prefixes[0], dg)) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; return true; }
-        out.dev.kind = VG_MATCH_EXACT; out.kind_name = "exact";
+        if (!decode_exact(format, prefixes[0], dg)) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; out.density = 0.0; return true; }
+        out.dev.kind = VG_MATCH_EXACT; out.kind_name = "exact"; out.density = 0.0;
         out.dev.exact_words = digest_len_of_format(format) / 4;
         for (int i = 0; i < 8; i++) out.dev.exact[i] = (uint32_t)dg[4 * i] | (uint32_t)dg[4 * i + 1] << 8 | (uint32_t)dg[4 * i + 2] << 16 | (uint32_t)dg[4 * i + 3] << 24;
         return true;
@@ -228,7 +228,7 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
         if (!merged.empty() && (r.first <= merged.back().second || r.first == merged.back().second + 1)) merged.back().second = std::max(merged.back().second, r.second);
         else merged.push_back(r);
     }
-    if (merged.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; return true; }   // e.g. ^3 on P2PKH
+    if (merged.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; out.density = 0.0; return true; }   // e.g. ^3 on P2PKH
     if (merged.size() > VG_MAX_INTERVALS) return true;   // too fragmented: keep the DFA path
     if (merged.size() == 1 && merged[0].first == 0 && merged[0].second == ~0ULL) {
         // the prefix constrains nothing (e.g. ^1 on P2PKH, ^bc1q on P2WPKH): only worth a prefilter if the rest does
@@ -237,6 +237,8 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
     }
     out.dev.kind = VG_MATCH_INTERVALS; out.kind_name = "intervals";
     out.dev.n_intervals = (int)merged.size();
+    out.density = 0.0;
+    for (auto &m : merged) out.density += ((double)(m.second - m.first) + 1.0) / 18446744073709551616.0;
     for (size_t i = 0; i < merged.size(); i++) {
         out.dev.lo_hi[i][0] = (uint32_t)(merged[i].first >> 32); out.dev.lo_hi[i][1] = (uint32_t)merged[i].first;
         out.dev.lo_hi[i][2] = (uint32_t)(merged[i].second >> 32); out.dev.lo_hi[i][3] = (uint32_t)merged[i].second;

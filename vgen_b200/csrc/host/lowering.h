@@ -13,6 +13,7 @@ struct LoweredPattern {
     Dfa dfa;                 // exact matcher on the address string (host confirm + device DFA path)
     PatternInfo info;
     vg_matcher_dev dev;      // device matcher (DFA table pointers are filled by the engine per device)
+    double density = 1.0;    // upper estimate of the fraction of keys the DEVICE matcher reports (1 = unknown / may be dense)
     std::string kind_name;   // "intervals" | "exact" | "dfa" | "all" | "none"
 };
 // shared-memory bytes the walk kernel needs to stage this DFA (table + accept + symbol classes), 0 if it is too large
