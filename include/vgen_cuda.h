@@ -96,8 +96,11 @@ int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t
 /* generate_batch (src/gpu.rs:660): hash160 of the compressed public key of n sequential scalars, 20 bytes
  * each; zeros for invalid scalars. */
 int vgen_cuda_hash160_batch(vgen_ctx *ctx, const uint8_t start_be[32], uint64_t n, uint8_t *out20);
-/* same for any format's digest, `stride` bytes per key (20, or 32 for P2TR's internal key) */
+/* same for any format's digest, `stride` bytes per key (20; 32 for P2TR, whose digest is the tweaked witness program) */
 int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride);
+/* format value accepted by vgen_cuda_digest_batch only: the P2TR internal key (x-only, even Y) BEFORE the TapTweak, 32 bytes per
+ * key — what the reference's dispatch_p2tr / await_result_p2tr return (src/gpu.rs:667-807) */
+#define VGEN_P2TR_INTERNAL_KEY 6
 
 /* Device-resident timing for bench.py: centres set up untimed, then n_windows full-size windows of the current
  * pattern timed with CUDA events on lane 0's stream. */

@@ -245,3 +245,23 @@ def test_dense_prefix_with_hit_limit_uses_small_windows(runner):
     cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=1, start=2**64, end=2**64 + 3 * runner.batch_size - 1)
     res = vg.scan_gpu_with_runner(vg.Pattern("^1CatDogCat"), cfg, None, None, runner)
     assert res.matches == [] and res.operations == 3 * runner.batch_size
+
+
+def test_dispatch_await_frames(small_runner):
+    """The reference's two-frame API (src/gpu.rs:535-658, 667-807): frames dispatched back to back, awaited in any order."""
+    r = small_runner
+    a, b = 2**64 + 7, 2**64 + 7 + r.batch_size
+    r.dispatch(a, 0)
+    r.dispatch(b, 1)
+    h1, s1 = r.await_result(1)
+    h0, s0 = r.await_result(0)
+    assert s0 == a.to_bytes(32, "big") and s1 == b.to_bytes(32, "big") and len(h0) == r.batch_size
+    assert b"".join(h0[:3000]) == oracle.hash160_batch(a, 3000) and b"".join(h1[-3000:]) == oracle.hash160_batch(b + r.batch_size - 3000, 3000)
+    # P2TR frame: the UNTWEAKED even-Y internal key = x of the public key
+    r.dispatch_p2tr(a, 0)
+    xs, _ = r.await_result_p2tr(0)
+    for i in (0, 1, 2, 1000, r.batch_size - 1):
+        assert int.from_bytes(xs[i], "big") == oracle.pubkey(a + i)[0]
+    res = vg.scan_gpu_p2tr_with_runner(vg.Pattern("^bc1pqq"), vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=0, start=a, end=a + (1 << 16)), None, None, r)
+    keys, _, _ = oracle.scan_range("p2tr", "^bc1pqq", a, (1 << 16) + 1)
+    assert [int(m.hex, 16) for m in res.matches] == keys and all(m.format == vg.AddressFormat.P2tr for m in res.matches)

@@ -221,7 +221,8 @@ bool Engine::launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uin
         uint32_t k8[8]; S.base.to_limbs32(k8);
         CK(cudaMemcpyAsync(S.d_base8, k8, 32, cudaMemcpyHostToDevice, L.stream));
         CK(launch_slow(fmt, mode, P, S.d_base8, L.d_pow2, 0xffffffffu, L.stream));
-        CK(launch_taptweak(mode, P, L.stream));
+        if (p2tr_internal_) CK(launch_dump_points_x(P, L.stream));
+        else CK(launch_taptweak(mode, P, L.stream));
         launches += 2; h2d_bytes += 32 + 2 * sizeof(vg_scan_params);
     }
     CK(cudaMemcpyAsync(S.h_counters, S.d_counters, kCounterWords * 4, cudaMemcpyDeviceToHost, L.stream));
@@ -394,8 +395,13 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
 }
 
 bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *out, uint32_t stride, std::string &err) {
+    // format 6 (VGEN_P2TR_INTERNAL_KEY): the untweaked even-Y internal key, as the reference's await_result_p2tr returns it
+    const bool internal = format == 6;
+    if (internal) format = VG_FMT_P2TR;
     if (format < 0 || format > 5 || stride == 0 || stride > 32) { err = "invalid format or stride"; return false; }
     if (n == 0) return true;
+    struct Flag { bool &f; ~Flag() { f = false; } } flag_guard{p2tr_internal_};
+    p2tr_internal_ = internal;
     if (n > (1ull << 28)) { err = "digest_batch is limited to 2^28 keys per call"; return false; }
     memset(out, 0, (size_t)n * stride);
     if (!(start <= secp_order_minus1())) return true;           // every scalar invalid: all zeros

@@ -86,6 +86,7 @@ private:
     uint32_t stride_lanes_ = 0;    // lane count the stride points were computed for
     LoweredPattern lp_;
     bool has_pattern_ = false;
+    bool p2tr_internal_ = false;   // digest_batch only: dump the untweaked internal keys instead of running the tweak stage
 };
 
 }  // namespace vg

@@ -18,6 +18,7 @@ cudaError_t launch_points_of_scalars(uint32_t *out, uint32_t n, const uint32_t *
 // P2TR: fixed-base table tab[256/bits][1 << bits][16] (v * 2^(bits*j) * G) and the stage-2 launch (taproot.cuh)
 cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2, cudaStream_t s);
 cudaError_t launch_taptweak(int mode, const vg_scan_params &P, cudaStream_t s);
+cudaError_t launch_dump_points_x(const vg_scan_params &P, cudaStream_t s);      // untweaked internal keys (x-only) of the window
 cudaError_t launch_walk(int fmt, int mode, const vg_scan_params &P, uint32_t blocks, cudaStream_t s);
 cudaError_t launch_slow(int fmt, int mode, const vg_scan_params &P, const uint32_t *base8_dev, const uint32_t *pow2,
                         uint32_t n_batches, cudaStream_t s);

@@ -50,6 +50,17 @@ __global__ void k_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *
     for (int l = 0; l < 8; l++) { tab[i * 16 + l] = x.v[l]; tab[i * 16 + 8 + l] = y.v[l]; }
 }
 
+// P2TR internal keys as the reference's dispatch_p2tr / await_result_p2tr return them (src/gpu.rs:667-807): the
+// big-endian x of the even-Y point, before the TapTweak. Reads stage 1's point buffer.
+__global__ void k_dump_points_x(const uint32_t *points, unsigned long long limit, uint8_t *out, uint32_t stride) {
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= limit) return;
+    for (uint32_t b = 0; b < stride && b < 32; b++) {
+        uint32_t w = points[i * 16 + (7 - (b >> 2))];
+        out[i * stride + b] = (uint8_t)(w >> (8 * (3 - (b & 3))));
+    }
+}
+
 #define VG_CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return e_; } while (0)
 
 cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, cudaStream_t s) {
@@ -61,6 +72,11 @@ cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, c
 cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2, cudaStream_t s) {
     const unsigned long long n = (256ull / bits) << bits;
     k_build_tap_table<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(tab, bits, pow2);
+    return cudaGetLastError();
+}
+cudaError_t launch_dump_points_x(const vg_scan_params &P, cudaStream_t s) {
+    if (P.limit == 0) return cudaSuccess;
+    k_dump_points_x<<<(unsigned)((P.limit + 255) / 256), 256, 0, s>>>(P.points, P.limit, P.dump, P.dump_stride);
     return cudaGetLastError();
 }
 cudaError_t launch_points_of_scalars(uint32_t *out, uint32_t n, const uint32_t *base8_dev, unsigned long long step,

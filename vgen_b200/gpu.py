@@ -5,6 +5,7 @@ import ctypes as C
 import enum
 import itertools
 import secrets
+import threading
 import time
 
 from . import _cabi
@@ -91,6 +92,54 @@ class GpuRunner:
         self._check(self._lib.vgen_cuda_hash160_batch(self._ctx, _be(start_key), n, buf))
         raw = buf.raw
         return [raw[20 * i:20 * i + 20] for i in range(n)]
+
+    # -- the reference's two-frame dispatch / await API (src/gpu.rs:535-658, 667-807). A frame is computed by a worker thread
+    # (ctypes releases the GIL); frames of one runner are serialised by a lock because a context runs one job at a time.
+    def _dispatch(self, kind, start_key, frame_index):
+        if frame_index not in (0, 1):
+            raise IndexError("frame_index must be 0 or 1")          # two frames in flight (src/gpu.rs:399)
+        if not hasattr(self, "_frames"):
+            self._frames, self._frame_lock = {}, threading.Lock()
+        box = {}
+
+        def work():
+            try:
+                with self._frame_lock:
+                    if kind == "p2tr":
+                        buf = C.create_string_buffer(32 * self.batch_size)
+                        self._check(self._lib.vgen_cuda_digest_batch(self._ctx, 6, _be(start_key), self.batch_size, buf, 32))
+                        raw = buf.raw
+                        box["out"] = [raw[32 * i:32 * i + 32] for i in range(self.batch_size)]
+                    else:
+                        box["out"] = self.generate_batch(start_key, self.batch_size)
+            except Exception as e:                                   # surfaced by await_result
+                box["err"] = e
+        t = threading.Thread(target=work, daemon=True)
+        t.start()
+        self._frames[(kind, frame_index)] = (t, box, _be(start_key))
+
+    def _await(self, kind, frame_index):
+        t, box, start = self._frames.pop((kind, frame_index))
+        t.join()
+        if "err" in box:
+            raise box["err"]
+        return box["out"], start
+
+    def dispatch(self, start_key, frame_index=0):
+        self._dispatch("h160", start_key, frame_index)
+
+    def await_result(self, frame_index=0):
+        """([hash160 bytes] * batch_size, start_key_bytes) of the frame (src/gpu.rs:602-658)."""
+        return self._await("h160", frame_index)
+
+    dispatch_batch_hash = dispatch                                   # src/gpu.rs:809: same result through the batch-inversion kernel
+
+    def dispatch_p2tr(self, start_key, frame_index=0):
+        self._dispatch("p2tr", start_key, frame_index)
+
+    def await_result_p2tr(self, frame_index=0):
+        """([32-byte x-only even-Y internal key] * batch_size, start_key_bytes): untweaked, as src/gpu.rs:750-807."""
+        return self._await("p2tr", frame_index)
 
     def digest_batch(self, fmt, start_key, n):
         fmt = AddressFormat.parse(fmt)
@@ -234,6 +283,18 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
     matches = MatchList(text, got, fmt)
     elapsed = time.perf_counter() - t0
     return ScanResult(matches=matches, operations=scanned, elapsed_secs=elapsed)
+
+
+def scan_gpu_p2tr_with_runner(pattern, config, progress_cb, stop, runner):
+    """src/gpu.rs:1168-1343. Here P2TR runs through the same entry point as every other format (both stages on the GPU)."""
+    import dataclasses
+    return scan_gpu_with_runner(pattern, dataclasses.replace(config, format=AddressFormat.P2tr), progress_cb, stop, runner)
+
+
+def scan_gpu_p2tr(pattern, config, progress_cb=None, stop=None):
+    """src/gpu.rs:1346-1366."""
+    import dataclasses
+    return scan_gpu(pattern, dataclasses.replace(config, format=AddressFormat.P2tr), progress_cb, stop)
 
 
 def scan_gpu(pattern, config, progress_cb=None, stop=None):
