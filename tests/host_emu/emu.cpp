@@ -14,6 +14,7 @@ static void ensure_pow2() { if (g_pow2.empty()) { g_pow2.resize(256 * 16); vg_bu
 
 extern "C" {
 void emu_fe_mul(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_mul(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }
+void emu_fe_sqr_fast(const uint32_t *a, uint32_t *r) { fe x, z; memcpy(x.v, a, 32); fe_sqr_fast(z, x); fe_canon(z); memcpy(r, z.v, 32); }
 void emu_fe_add(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_add(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }
 void emu_fe_sub(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_sub(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }
 void emu_fe_inv(const uint32_t *a, uint32_t *r) { fe x, z; memcpy(x.v, a, 32); fe_inv(z, x); fe_canon(z); memcpy(r, z.v, 32); }

@@ -47,6 +47,11 @@ def test_field_ops(emu):
         emu.emu_fe_mul(limbs(a), limbs(b), out); assert val(out) == a * b % P
         emu.emu_fe_add(limbs(a), limbs(b), out); assert val(out) == (a + b) % P
         emu.emu_fe_sub(limbs(a), limbs(b), out); assert val(out) == (a - b) % P
+        emu.emu_fe_sqr_fast(limbs(a), out); assert val(out) == a * a % P, hex(a)
+    # squaring: carry patterns (all-ones limbs, single limbs, alternating)
+    for a in [2**256 - 1, 2**224 - 1, (2**32 - 1) << 96, sum((2**32 - 1) << (64 * i) for i in range(4)), sum((2**32 - 1) << (64 * i + 32) for i in range(4)),
+              0xFFFFFFFF00000001FFFFFFFF00000001FFFFFFFF00000001FFFFFFFF00000001] + [rng.getrandbits(256) | (2**256 - 2**200) for _ in range(50)]:
+        emu.emu_fe_sqr_fast(limbs(a), out); assert val(out) == a * a % P, hex(a)
     for a in edge[1:4] + vals[12:40]:
         if a % P == 0:
             continue

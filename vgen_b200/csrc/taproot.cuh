@@ -44,13 +44,13 @@ VG_DEV bool vg_tweak_is_valid(const uint32_t t[8]) {
 // their x coordinate (doubling / opposite points): the caller then redoes the key with the complete formulas.
 VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
     fe z2, u2, s2, h, rr, h2, h3, v, t;
-    fe_sqr(z2, a.z); fe_mul(u2, bx, z2);
+    fe_sqr_fast(z2, a.z); fe_mul(u2, bx, z2);
     fe_mul(s2, by, z2); fe_mul(s2, s2, a.z);
     fe_sub(h, u2, a.x); fe_sub(rr, s2, a.y);
     fe hc = h; fe_canon(hc);
     if (fe_is_zero_raw(hc)) return false;
-    fe_sqr(h2, h); fe_mul(h3, h2, h); fe_mul(v, a.x, h2);
-    fe_sqr(t, rr); fe_sub(t, t, h3); fe_sub(t, t, v); fe_sub(t, t, v);      // X3
+    fe_sqr_fast(h2, h); fe_mul(h3, h2, h); fe_mul(v, a.x, h2);
+    fe_sqr_fast(t, rr); fe_sub(t, t, h3); fe_sub(t, t, v); fe_sub(t, t, v);      // X3
     fe_sub(v, v, t); fe_mul(v, rr, v); fe_mul(h3, a.y, h3); fe_sub(a.y, v, h3);
     a.x = t;
     fe_mul(a.z, a.z, h);
@@ -133,7 +133,7 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
             // all threads walk the table loop together (barriers inside); invalid keys skip the additions
             if (!vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits, ok) && ok)
                 ok = vg_tap_output_key_slow(q, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
-            if (ok) { X[k] = q.x; fe_sqr(z2, q.z); }
+            if (ok) { X[k] = q.x; fe_sqr_fast(z2, q.z); }
         }
         if (ok) ok_mask |= 1u << k;
         Z2[k] = z2;
