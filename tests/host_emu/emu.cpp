@@ -22,6 +22,24 @@ int emu_scalar_mul(const uint32_t *k, uint32_t *x, uint32_t *y) {
     ensure_pow2(); fe fx, fy; bool ok = scalar_is_valid(k) && scalar_mul_pow2(fx, fy, k, g_pow2.data());
     memcpy(x, fx.v, 32); memcpy(y, fy.v, 32); return ok ? 0 : -1;
 }
+// the device's 8-bit windowed k*G (ec.cuh scalar_mul_G with w8 = true); builds the win8 part of the table on first use
+static std::vector<uint32_t> g_gtable;
+int emu_scalar_mul_w8(const uint32_t *k, uint32_t *x, uint32_t *y) {
+    ensure_pow2();
+    if (g_gtable.empty()) {
+        g_gtable.assign(VG_GTABLE_WORDS, 0);
+        memcpy(g_gtable.data(), g_pow2.data(), VG_GTABLE_POW2_WORDS * 4);
+        for (uint32_t i = 0; i < 32 * 256; i++) {
+            uint32_t j = i >> 8, v = i & 255u, kk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            if (!v) continue;
+            kk[j >> 2] = v << (8 * (j & 3));
+            fe px, py; scalar_mul_pow2(px, py, kk, g_pow2.data());
+            memcpy(&g_gtable[VG_GTABLE_POW2_WORDS + (size_t)i * 16], px.v, 32); memcpy(&g_gtable[VG_GTABLE_POW2_WORDS + (size_t)i * 16 + 8], py.v, 32);
+        }
+    }
+    fe fx, fy; bool ok = scalar_is_valid(k) && scalar_mul_G(fx, fy, k, g_gtable.data(), true);
+    memcpy(x, fx.v, 32); memcpy(y, fy.v, 32); return ok ? 0 : -1;
+}
 void emu_digest(int fmt, const uint32_t *x, const uint32_t *y, uint32_t *dg) {
     fe fx, fy; memcpy(fx.v, x, 32); memcpy(fy.v, y, 32);
     switch (fmt) {

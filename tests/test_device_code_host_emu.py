@@ -22,7 +22,7 @@ P_FIELD = 2**256 - 2**32 - 977
 @pytest.fixture(scope="module")
 def emu():
     csrc = os.path.join(HERE, "..", "vgen_b200", "csrc")
-    deps = [SRC] + [os.path.join(csrc, f) for f in ("fe.cuh", "ec.cuh", "hash.cuh", "scan_core.cuh", "match.cuh", "taproot.cuh", "scan_types.h")]
+    deps = [SRC] + [os.path.join(csrc, f) for f in ("fe.cuh", "ec.cuh", "hash.cuh", "scan_core.cuh", "match.cuh", "taproot.cuh", "scan_types.h", "kernels.h")]
     deps = [d for d in deps if os.path.exists(d)]
     if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", "-fPIC", "-shared", "-o", LIB, SRC])
@@ -67,6 +67,19 @@ def test_scalar_mul_vs_oracle(emu):
         assert (val(x), val(y)) == oracle.pubkey(k)
     for k in [0, N, N + 1, 2**256 - 1]:
         assert emu.emu_scalar_mul(limbs(k), x, y) != 0
+
+
+def test_windowed_scalar_mul_vs_oracle(emu):
+    """ec.cuh scalar_mul_G (8-bit windows: centre set-up and degenerate-batch path on the device) == the oracle's k*G."""
+    rng = random.Random(3)
+    x = (C.c_uint32 * 8)(); y = (C.c_uint32 * 8)()
+    ks = [1, 2, 255, 256, 257, 2**8 - 1, 2**64, 2**255, N - 1, N - 2, 0xFF00FF00FF00FF00FF00FF00FF00FF00FF00FF00FF00FF00FF00FF00FF00FF00 % N,
+          (N + 1) // 2] + [rng.randrange(1, N) for _ in range(30)]
+    for k in ks:
+        assert emu.emu_scalar_mul_w8(limbs(k), x, y) == 0
+        assert (val(x), val(y)) == oracle.pubkey(k), hex(k)
+    for k in [0, N, 2**256 - 1]:
+        assert emu.emu_scalar_mul_w8(limbs(k), x, y) != 0
 
 
 @pytest.mark.parametrize("fmt", [0, 1, 2, 3, 5])

@@ -98,6 +98,34 @@ VG_COLD bool scalar_mul_pow2(fe &x, fe &y, const uint32_t k[8], const uint32_t *
     }
     return gej_to_affine(x, y, acc);
 }
+// Generator tables in one device buffer: pow2[256][16] (2^i * G) followed by win8[32][256][16] (v * 2^(8j) * G, v = 0 unused).
+#define VG_GTABLE_POW2_WORDS (256 * 16)
+#ifndef VG_GTABLE_WORDS
+#define VG_GTABLE_WORDS (VG_GTABLE_POW2_WORDS + 32 * 256 * 16)
+#endif
+// k*G by 8-bit windows: at most 32 additions (the bit-by-bit table above needs ~128). Used for the centre set-up of every
+// scan (one scalar multiplication per thread, replacing the host-side key_to_affine of src/gpu.rs:901-910) and for the
+// degenerate-batch path. w8 = false falls back to the pow2 table (host emulation builds only that part by default).
+VG_COLD bool scalar_mul_G(fe &x, fe &y, const uint32_t k[8], const uint32_t *gtable, bool w8) {
+    if (!w8) return scalar_mul_pow2(x, y, k, gtable);
+    const uint32_t *win8 = gtable + VG_GTABLE_POW2_WORDS;
+    gej_t acc; acc.inf = true;
+    fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
+    for (int j = 0; j < 32; j++) {
+        const uint32_t v = (k[j >> 2] >> (8 * (j & 3))) & 0xffu;
+        if (!v) continue;
+        const uint32_t *e = win8 + ((size_t)j * 256 + v) * 16;
+        fe bx, by;
+        VG_UNROLL for (int l = 0; l < 8; l++) { bx.v[l] = e[l]; by.v[l] = e[8 + l]; }
+        gej_t nr; gej_add_affine(nr, acc, bx, by); acc = nr;
+    }
+    return gej_to_affine(x, y, acc);
+}
+#ifdef VG_HOST_EMU
+#define VG_W8 false
+#else
+#define VG_W8 true
+#endif
 // affine add given inv = 1/(bx - ax): (x3, y3) = (ax, ay) + (bx, by). 2M + 1S. Outputs weakly reduced.
 VG_DEV void affine_add_inv(fe &x3, fe &y3, const fe &ax, const fe &ay, const fe &bx, const fe &by, const fe &inv) {
     fe dy, lam, t;

@@ -77,7 +77,7 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
         CK(cudaSetDevice(L.device));
         CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&L.copy_stream, cudaStreamNonBlocking));
-        CK(cudaMalloc(&L.d_pow2, 256 * 16 * 4));
+        CK(cudaMalloc(&L.d_pow2, (size_t)VG_GTABLE_WORDS * 4));       // pow2[256] + win8[32][256] (ec.cuh)
         CK(cudaMalloc(&L.d_gtab, (size_t)half_ * 16 * 4));
         CK(cudaMalloc(&L.d_centers, (size_t)16 * F.threads * 4));
         CK(cudaMalloc(&L.d_scratch, (size_t)(half_ + 1) * 8 * F.threads * 4));
@@ -94,7 +94,7 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
         L.h_hits_cap = 1u << 20;
         CK(cudaHostAlloc(&L.h_hits, L.h_hits_cap * sizeof(vg_hit_rec), cudaHostAllocDefault));
         CK(launch_build_tables(L.d_pow2, L.d_gtab, half_, L.stream));
-        launches += 2;
+        launches += 3;
         CK(cudaStreamSynchronize(L.stream));
     }
     return true;

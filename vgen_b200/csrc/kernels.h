@@ -11,6 +11,10 @@
 #define VG_CTAS_PER_SM 2
 #endif
 
+// words of the generator table buffer (pow2[256][16] + win8[32][256][16]); must match ec.cuh
+#ifndef VG_GTABLE_WORDS
+#define VG_GTABLE_WORDS (256 * 16 + 32 * 256 * 16)
+#endif
 namespace vg {
 cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, cudaStream_t s);
 cudaError_t launch_points_of_scalars(uint32_t *out, uint32_t n, const uint32_t *base8_dev, unsigned long long step,

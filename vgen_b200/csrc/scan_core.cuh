@@ -259,9 +259,9 @@ VG_DEV void vg_build_pow2(uint32_t *pow2, const uint32_t gxy[16]) {
     }
 }
 // affine point of scalar base + mul*tid + add, stored limb-major at column tid of out[16][n]; zeros if invalid
-VG_DEV void vg_point_of_scalar(uint32_t *out, uint32_t n, uint32_t col, const uint32_t k[8], const uint32_t *pow2) {
+VG_DEV void vg_point_of_scalar(uint32_t *out, uint32_t n, uint32_t col, const uint32_t k[8], const uint32_t *pow2, bool w8 = VG_W8) {
     fe x, y;
-    bool ok = scalar_is_valid(k) && scalar_mul_pow2(x, y, k, pow2);
+    bool ok = scalar_is_valid(k) && scalar_mul_G(x, y, k, pow2, w8);
     if (!ok) { fe_set_zero(x); fe_set_zero(y); }
     VG_STORE_FE(out + col, n, x);
     VG_STORE_FE(out + (size_t)8 * n + col, n, y);
@@ -270,7 +270,7 @@ VG_DEV void vg_point_of_scalar(uint32_t *out, uint32_t n, uint32_t col, const ui
 template <int FMT, int MODE>
 VG_DEV void vg_slow_key(const vg_scan_params &P, const vg_dfa_view &dv, const uint32_t k[8], unsigned long long idx, const uint32_t *pow2) {
     fe x, y;
-    bool ok = scalar_is_valid(k) && scalar_mul_pow2(x, y, k, pow2);
+    bool ok = scalar_is_valid(k) && scalar_mul_G(x, y, k, pow2, VG_W8);
     if (!ok) { fe_set_zero(x); fe_set_zero(y); }
     vg_process_point<FMT, MODE>(P, dv, x, y, idx, ok);
 }

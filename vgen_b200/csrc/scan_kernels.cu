@@ -25,6 +25,19 @@ __global__ void k_points_of_scalars(uint32_t *out, uint32_t n, const uint32_t *b
     scalar_add_u64(k, b, (unsigned long long)t * step);
     vg_point_of_scalar(out, n, t, k, pow2);
 }
+// win8[j][v][16] = (v << 8j) * G behind the pow2 part of the generator table (ec.cuh: scalar_mul_G)
+__global__ void k_build_win8(uint32_t *gtable) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= 32 * 256) return;
+    uint32_t j = i >> 8, v = i & 255u;
+    uint32_t k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    k[j >> 2] = v << (8 * (j & 3));
+    fe x, y;
+    bool ok = v != 0 && scalar_mul_pow2(x, y, k, gtable);
+    if (!ok) { fe_set_zero(x); fe_set_zero(y); }
+    uint32_t *o = gtable + VG_GTABLE_POW2_WORDS + (size_t)i * 16;
+    for (int l = 0; l < 8; l++) { o[l] = x.v[l]; o[8 + l] = y.v[l]; }
+}
 // gtab[i][16] = (i+1)*G, point-major (x limbs then y limbs)
 __global__ void k_build_gtab(uint32_t *gtab, uint32_t half, const uint32_t *pow2) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -65,6 +78,8 @@ __global__ void k_dump_points_x(const uint32_t *points, unsigned long long limit
 
 cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, cudaStream_t s) {
     k_build_pow2<<<1, 32, 0, s>>>(pow2);
+    VG_CK(cudaGetLastError());
+    k_build_win8<<<64, 128, 0, s>>>(pow2);
     VG_CK(cudaGetLastError());
     k_build_gtab<<<(half + 127) / 128, 128, 0, s>>>(gtab, half, pow2);
     return cudaGetLastError();
