@@ -341,6 +341,9 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         }
         const U256 base = S.base;
         const bool with_text = n_hits <= kEagerTextHits;
+        // records in key order (the device appends them in atomic order): slices then come out ascending and consecutive, so the
+        // hit list stays sorted as windows are collected and the final sort is a no-op check
+        std::sort(recs->begin(), recs->end(), [](const vg_hit_rec &a, const vg_hit_rec &b) { return a.idx_hi != b.idx_hi ? a.idx_hi < b.idx_hi : a.idx_lo < b.idx_lo; });
         // big windows are confirmed in up to 4 slices so that the last window's job is not a serial tail
         const size_t n_rec = recs->size();
         const size_t n_slices = n_rec >= 256 ? 4 : 1;
@@ -389,7 +392,8 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
     }
     drain(false);
     for (auto &L : lanes_) { CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); L.centers_level = -1; }
-    std::sort(hits.begin(), hits.end(), [](const Hit &a, const Hit &b) { return a.key < b.key; });
+    auto by_key = [](const Hit &a, const Hit &b) { return a.key < b.key; };
+    if (!std::is_sorted(hits.begin(), hits.end(), by_key)) std::sort(hits.begin(), hits.end(), by_key);
     if (max_hits && hits.size() > max_hits) hits.resize(max_hits);
     return true;
 }
