@@ -118,6 +118,9 @@ def _check_scan(runner, fmt, pat, start, n, ci=False):
     ("ethereum", "^0xdea", False), ("ethereum", "^0xDe", False), ("ethereum", "^0xab", True), ("ethereum", "F00$", False),
     ("p2tr", "^bc1pqq", False), ("p2tr", "dead$", False), ("p2tr", "^bc1p.*zzz", False), ("p2tr", "^bc1q", False),
     ("p2pkh", "abc$", False), ("p2pkh", "[0-9]{4}$", False), ("p2pkh", "^1.*XYZ", False), ("p2pkh", "^3", False),
+    # anchored alternations / optional tails: prefixes read off the DFA become digest intervals (lowering.cpp)
+    ("p2pkh", "^(1Ca|1Do)", False), ("p2pkh", "^1(Ca|Do)t?x", False), ("p2wpkh", "^bc1q(aa|zz)", False),
+    ("ethereum", "^0x(de|be)a", False), ("p2tr", "^bc1p(qq|pp)", False), ("p2sh-p2wpkh", "^(3Ab|3Cd)$", False),
 ])
 def test_scan_match_sets_small(small_runner, fmt, pat, ci):
     _check_scan(small_runner, fmt, pat, 2**64, 1 << 18, ci)

@@ -90,6 +90,45 @@ def test_lowering_kinds():
     assert vg.Pattern(r"^1BgGZ9tcN4rm9KBzDn7KprQz87SZ26SAMh$").lowering(F.P2pkh)["kind"] == "none"   # bad checksum
 
 
+def test_lowering_alternations_read_off_the_dfa():
+    """Anchored patterns that are not a plain run of character sets (alternations, optional tails) still become
+    digest-interval prefilters: the prefixes are read off the compiled DFA (lowering.cpp derive_prefixes_from_dfa)."""
+    F = vg.AddressFormat
+    cases = [
+        (F.P2pkh, "^(1Cat|1Dog)", "intervals", 4), (F.P2pkh, "^1(Cat|Dog)s?", "intervals", 4),
+        (F.P2wpkh, "^bc1q(aa|zz)", "intervals", 2), (F.Ethereum, "^0x(dead|beef)", "intervals", 2),
+        (F.P2tr, "^bc1p(q|p)q", "intervals", 2), (F.P2pkh, "(1Cat|1Dog)", "dfa", None),
+        (F.P2pkh, "^(3Cat|3Dog)", "none", None), (F.P2pkh, "^1.*x", "dfa", None),
+        (F.P2pkh, "^(1BgGZ9tcN4rm9KBzDn7KprQz87SZ26SAMH|1CUNEBjYrCn2y1SdiUMohaKUi4wpP326Lb)$", "intervals", 2),
+    ]
+    for fmt, pat, kind, n in cases:
+        low = vg.Pattern(pat).lowering(fmt)
+        assert low["kind"] == kind, (pat, low)
+        if n is not None:
+            assert len(low["intervals"]) == n, (pat, low)
+    # the union of the branches' intervals equals the alternation's intervals
+    a = vg.Pattern("^1Cat").lowering(F.P2pkh)["intervals"]
+    b = vg.Pattern("^1Dog").lowering(F.P2pkh)["intervals"]
+    assert sorted(a + b) == sorted(vg.Pattern("^(1Cat|1Dog)").lowering(F.P2pkh)["intervals"])
+
+
+@pytest.mark.parametrize("fmt", ["p2pkh", "p2wpkh", "p2sh-p2wpkh", "ethereum"])
+def test_alternation_intervals_are_a_superset(fmt, golden):
+    """Completeness of the DFA-derived prefilter: every golden address is accepted by ^(own prefix|other prefix)."""
+    F = vg.AddressFormat.parse(fmt)
+    vs = golden["vectors"][:30]
+    for i, v in enumerate(vs):
+        addr, dg = v[fmt]["address"], bytes.fromhex(v[fmt]["digest"])
+        other = vs[(i + 7) % len(vs)][fmt]["address"]
+        for n in (3, 5, 7, 10):
+            pat = "^(" + re.escape(other[:n]) + "|" + re.escape(addr[:n]) + ")"
+            p = vg.Pattern(pat)
+            assert p.matches(addr)
+            low = p.lowering(F)
+            assert low["kind"] in ("intervals", "all"), (pat, low)
+            assert _covered(low, dg), (pat, low)
+
+
 def _covered(low, digest):
     if low["kind"] in ("all", "dfa"):
         return True

@@ -173,6 +173,53 @@ void fill_device_dfa(int format, const Dfa &dfa, vg_dfa_dev &d) {
             break;
     }
 }
+
+// Literal prefixes read off the DFA itself, for anchored patterns whose syntax tree is not a plain run of character sets
+// (alternations such as ^(1Cat|1Dog), optional groups, ...): breadth-first over the format's alphabet from the start
+// state, dropping transitions into dead states (no accepting state reachable) and closing a prefix when its state is
+// universal (everything reachable accepts). Stops growing when more than 64 prefixes would be live; what is returned is
+// then a necessary condition only (`complete` = false) and the host confirmation decides.
+bool derive_prefixes_from_dfa(const Dfa &d, const char *alpha, std::vector<std::string> &prefixes, bool &complete) {
+    const uint32_t ns = d.n_states, nc = d.n_classes;
+    std::vector<uint8_t> live(ns, 0), universal(ns, 1);
+    for (uint32_t s = 0; s < ns; s++) live[s] = d.accept_end[s] != 0;
+    for (bool ch = true; ch;) {                 // live: an accepting state is reachable
+        ch = false;
+        for (uint32_t s = 0; s < ns; s++) if (!live[s]) for (uint32_t c = 0; c < nc; c++) if (live[d.table[(size_t)s * nc + c]]) { live[s] = 1; ch = true; break; }
+    }
+    for (uint32_t s = 0; s < ns; s++) universal[s] = d.accept_end[s] != 0;
+    for (bool ch = true; ch;) {                 // universal: accepting, and every successor universal
+        ch = false;
+        for (uint32_t s = 0; s < ns; s++) if (universal[s]) for (uint32_t c = 0; c < nc; c++) if (!universal[d.table[(size_t)s * nc + c]]) { universal[s] = 0; ch = true; break; }
+    }
+    if (!live[d.start]) { prefixes.clear(); complete = true; return true; }     // can never match
+    std::string chars;
+    for (const char *a = alpha; *a; a++) if (chars.find(*a) == std::string::npos) chars.push_back(*a);
+    std::vector<std::pair<uint32_t, std::string>> frontier{{d.start, ""}};
+    std::vector<std::string> closed;
+    complete = true;
+    for (int depth = 0; depth < 64 && !frontier.empty(); depth++) {
+        std::vector<std::pair<uint32_t, std::string>> next;
+        std::vector<std::string> closed_next = closed;
+        for (auto &f : frontier) {
+            if (universal[f.first]) { closed_next.push_back(f.second); continue; }
+            if (d.accept_end[f.first]) { closed_next.push_back(f.second); complete = false; }     // the address may END here ("...$")
+            for (char c : chars) {
+                uint32_t t = d.table[(size_t)f.first * nc + d.class_of[(uint8_t)c]];
+                if (live[t]) next.push_back({t, f.second + c});
+            }
+        }
+        if (closed_next.size() + next.size() > 64) { complete = false; break; }
+        closed.swap(closed_next);
+        frontier.swap(next);
+    }
+    prefixes = closed;
+    for (auto &f : frontier) {
+        prefixes.push_back(f.second);
+        if (!universal[f.first]) complete = false;      // e.g. "...$": the string must END here; the prefix alone does not decide
+    }
+    return !(prefixes.size() == 1 && prefixes[0].empty());
+}
 }  // namespace
 
 uint32_t dfa_smem_bytes(const vg_dfa_dev &d) {
@@ -181,7 +228,40 @@ uint32_t dfa_smem_bytes(const vg_dfa_dev &d) {
     return bytes <= 64 * 1024 ? (uint32_t)bytes : 0;
 }
 
-bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPattern &out, std::string &err) {
+// prefixes -> merged inclusive intervals over the leading 64 digest bits -> device matcher (kind stays DFA when useless)
+// `decides`: the prefixes are the whole pattern (nothing follows them), so an unconstrained prefix means "match all"
+static bool intervals_from_prefixes(int format, const std::vector<std::string> &prefixes, bool decides, LoweredPattern &out) {
+    std::vector<Range> ranges;
+    for (const auto &p : prefixes) ranges_for(format, p, ranges);
+    // reduce to the leading 64 digest bits, merge
+    unsigned bits = format == VG_FMT_P2TR ? 256 : 160;
+    std::vector<std::pair<uint64_t, uint64_t>> r64;
+    for (auto &r : ranges) r64.push_back({r.first.shr(bits - 64).w[0], r.second.shr(bits - 64).w[0]});
+    std::sort(r64.begin(), r64.end());
+    std::vector<std::pair<uint64_t, uint64_t>> merged;
+    for (auto &r : r64) {
+        if (!merged.empty() && (r.first <= merged.back().second || r.first == merged.back().second + 1)) merged.back().second = std::max(merged.back().second, r.second);
+        else merged.push_back(r);
+    }
+    if (merged.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; out.density = 0.0; return true; }   // e.g. ^3 on P2PKH
+    if (merged.size() > VG_MAX_INTERVALS) return true;   // too fragmented: keep the DFA path
+    if (merged.size() == 1 && merged[0].first == 0 && merged[0].second == ~0ULL) {
+        // the prefix constrains nothing (e.g. ^1 on P2PKH, ^bc1q on P2WPKH): only worth a prefilter if the rest does
+        if (decides) { out.dev.kind = VG_MATCH_ALL; out.kind_name = "all"; }
+        return true;
+    }
+    out.dev.kind = VG_MATCH_INTERVALS; out.kind_name = "intervals";
+    out.dev.n_intervals = (int)merged.size();
+    out.density = 0.0;
+    for (auto &m : merged) out.density += ((double)(m.second - m.first) + 1.0) / 18446744073709551616.0;
+    for (size_t i = 0; i < merged.size(); i++) {
+        out.dev.lo_hi[i][0] = (uint32_t)(merged[i].first >> 32); out.dev.lo_hi[i][1] = (uint32_t)merged[i].first;
+        out.dev.lo_hi[i][2] = (uint32_t)(merged[i].second >> 32); out.dev.lo_hi[i][3] = (uint32_t)merged[i].second;
+    }
+    return true;
+}
+
+static bool lower_syntactic(int format, const std::string &pattern, bool ci, LoweredPattern &out, std::string &err) {
     out = LoweredPattern();
     out.format = format; out.pattern = pattern; out.case_insensitive = ci;
     if (format < 0 || format > 5) { err = "invalid address format"; return false; }
@@ -216,34 +296,18 @@ bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPatte
         for (int i = 0; i < 8; i++) out.dev.exact[i] = (uint32_t)dg[4 * i] | (uint32_t)dg[4 * i + 1] << 8 | (uint32_t)dg[4 * i + 2] << 16 | (uint32_t)dg[4 * i + 3] << 24;
         return true;
     }
-    std::vector<Range> ranges;
-    for (const auto &p : prefixes) ranges_for(format, p, ranges);
-    // reduce to the leading 64 digest bits, merge
-    unsigned bits = format == VG_FMT_P2TR ? 256 : 160;
-    std::vector<std::pair<uint64_t, uint64_t>> r64;
-    for (auto &r : ranges) r64.push_back({r.first.shr(bits - 64).w[0], r.second.shr(bits - 64).w[0]});
-    std::sort(r64.begin(), r64.end());
-    std::vector<std::pair<uint64_t, uint64_t>> merged;
-    for (auto &r : r64) {
-        if (!merged.empty() && (r.first <= merged.back().second || r.first == merged.back().second + 1)) merged.back().second = std::max(merged.back().second, r.second);
-        else merged.push_back(r);
-    }
-    if (merged.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; out.density = 0.0; return true; }   // e.g. ^3 on P2PKH
-    if (merged.size() > VG_MAX_INTERVALS) return true;   // too fragmented: keep the DFA path
-    if (merged.size() == 1 && merged[0].first == 0 && merged[0].second == ~0ULL) {
-        // the prefix constrains nothing (e.g. ^1 on P2PKH, ^bc1q on P2WPKH): only worth a prefilter if the rest does
-        if (info.rest_empty && !truncated) { out.dev.kind = VG_MATCH_ALL; out.kind_name = "all"; }
-        return true;
-    }
-    out.dev.kind = VG_MATCH_INTERVALS; out.kind_name = "intervals";
-    out.dev.n_intervals = (int)merged.size();
-    out.density = 0.0;
-    for (auto &m : merged) out.density += ((double)(m.second - m.first) + 1.0) / 18446744073709551616.0;
-    for (size_t i = 0; i < merged.size(); i++) {
-        out.dev.lo_hi[i][0] = (uint32_t)(merged[i].first >> 32); out.dev.lo_hi[i][1] = (uint32_t)merged[i].first;
-        out.dev.lo_hi[i][2] = (uint32_t)(merged[i].second >> 32); out.dev.lo_hi[i][3] = (uint32_t)merged[i].second;
-    }
-    return true;
+    return intervals_from_prefixes(format, prefixes, info.rest_empty && !truncated, out);
+}
+
+bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPattern &out, std::string &err) {
+    if (!lower_syntactic(format, pattern, ci, out, err)) return false;
+    if (out.dev.kind != VG_MATCH_DFA || !out.info.anchored_start) return true;
+    // anchored, but the leading run of character sets decided nothing (alternations such as ^(1Cat|1Dog), ^bc1q(aa|zz),
+    // optional groups): take the prefixes from the DFA. Superset semantics: the host confirmation decides.
+    std::vector<std::string> pf; bool complete = false;
+    if (!derive_prefixes_from_dfa(out.dfa, alphabet_for(format), pf, complete)) return true;
+    if (pf.empty()) { out.dev.kind = VG_MATCH_INTERVALS; out.dev.n_intervals = 0; out.kind_name = "none"; out.density = 0.0; return true; }
+    return intervals_from_prefixes(format, pf, complete, out);
 }
 
 }  // namespace vg
