@@ -65,12 +65,11 @@ static std::vector<uint32_t> g_tap; static uint32_t g_tap_bits = 0;
 void emu_tap_stage2(uint32_t *points, uint32_t n, uint32_t bits, uint8_t *out32) {
     ensure_pow2();
     if (g_tap_bits != bits) {
-        const size_t cnt = (size_t)(256 / bits) << bits;
+        const size_t cnt = (size_t)vg_tap_windows(bits) << bits;
         g_tap.assign(cnt * 16, 0);
         for (size_t i = 0; i < cnt; i++) {
-            uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1u << bits) - 1)), k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-            if (!v) continue;
-            k[(j * bits) >> 5] = v << ((j * bits) & 31u);
+            uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1u << bits) - 1)), k[8];
+            if (!vg_tap_digit_scalar(k, j, v, bits)) continue;
             fe x, y; scalar_mul_pow2(x, y, k, g_pow2.data());
             memcpy(&g_tap[i * 16], x.v, 32); memcpy(&g_tap[i * 16 + 8], y.v, 32);
         }

@@ -148,7 +148,7 @@ def test_p2tr_stage2_invalid_points_and_small_tweak_table(emu):
             for l in range(8):
                 pts[16 * i + l] = (x >> (32 * l)) & 0xffffffff
                 pts[16 * i + 8 + l] = (y >> (32 * l)) & 0xffffffff
-    for bits in (4, 8):
+    for bits in (4, 8, 5, 7):       # 5 and 7: digits straddle 32-bit limbs and the top window is partial (as with 24-bit windows)
         out = C.create_string_buffer(32 * len(ks))
         emu.emu_tap_stage2(pts, len(ks), bits, out)
         for i, k in enumerate(ks):

@@ -8,9 +8,11 @@
 // device-to-device traffic, and hits come back in ascending key order.
 #include "engine.h"
 #include <algorithm>
+#include <chrono>
 #include <deque>
 #include <future>
 #include <string.h>
+#include <stdio.h>
 #include <stdlib.h>
 
 namespace vg {
@@ -130,7 +132,15 @@ bool Engine::upload_dfa(std::string &err) {
     return true;
 }
 
-static const uint32_t kTapBits = 16;     // 16 windows of 16 bits: 16 x 65536 x 64 B = 64 MiB, resident in the 126 MB L2
+// Window width of the P2TR fixed-base table. 16: 16 windows x 65,536 x 64 B = 64 MiB, resident in the 126 MB L2.
+// VGEN_TAP_BITS overrides (4..26; 24 = 11 windows x 16 Mi x 64 B = 11 GiB gathered from HBM, 5 additions fewer per key).
+static uint32_t tap_bits_from_env() {
+    const char *e = getenv("VGEN_TAP_BITS");
+    long v = e ? strtol(e, nullptr, 10) : 16;
+    return (uint32_t)(v < 4 ? 4 : v > 26 ? 26 : v);
+}
+static const uint32_t kTapBits = tap_bits_from_env();
+static size_t tap_table_bytes(uint32_t bits) { return ((size_t)((256 + bits - 1) / bits) << bits) * 64; }
 
 // P2TR needs two more buffers per lane: the stage-1 -> stage-2 point buffer (64 B per window key) and the
 // fixed-base table of the tweak addition. Allocated and built on first use.
@@ -142,7 +152,7 @@ bool Engine::ensure_taproot(std::string &err) {
         CK(cudaMalloc(&L.d_points, (size_t)F.window * 64));
         for (auto &O : lanes_) if (&O != &L && O.device == L.device && O.d_tap_table) L.d_tap_table = O.d_tap_table;   // one table per GPU
         if (L.d_tap_table) continue;
-        CK(cudaMalloc(&L.d_tap_table, ((size_t)(256 / kTapBits) << kTapBits) * 64));
+        CK(cudaMalloc(&L.d_tap_table, tap_table_bytes(kTapBits)));
         L.owns_tap_table = true;
         CK(launch_build_tap_table(L.d_tap_table, kTapBits, L.d_pow2, L.stream));
         launches++;
@@ -254,7 +264,14 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         return true;
     }
     const U256 N = end.sub(start).add64(1);            // >= 1; cannot wrap because end <= n-1 < 2^256-1
+    // VGEN_TRACE=1: phase timestamps of this call on stderr (ms since entry)
+    static const bool trace = getenv("VGEN_TRACE") != nullptr;
+    const auto t_entry = std::chrono::steady_clock::now();
+    auto mark = [&](const char *what) {
+        if (trace) fprintf(stderr, "[vgen trace] %-22s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_entry).count());
+    };
     if (!compute_stride_points(err)) return false;
+    mark("stride points");
     const uint32_t nl = (uint32_t)lanes_.size(), G = shard_count_ * nl;
     const int fl = (int)levels_.size() - 1;
     // ramp levels (small windows first) only when the scan is likely to end early: a hit limit, and a device matcher
@@ -380,9 +397,12 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
 
     bool stopping = false;
     for (int round = 0; round < 2; round++) for (uint32_t li = 0; li < nl; li++) if (!issue(li)) return false;
+    mark("first windows issued");
+    uint64_t n_collected = 0;
     while (!inflight.empty()) {
         auto [li, s] = inflight.front(); inflight.pop_front();
         if (!collect(li, s, !stopping)) return false;
+        if (trace && (n_collected++ < 3 || inflight.size() < 3)) mark("window collected");
         if (!stopping) {
             if (progress) progress(keys_scanned);
             if (stop && *stop) stopping = true;
@@ -390,11 +410,14 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         }
         if (!stopping && !issue(li)) return false;
     }
+    mark("all windows collected");
     drain(false);
+    mark("confirm jobs drained");
     for (auto &L : lanes_) { CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); L.centers_level = -1; }
     auto by_key = [](const Hit &a, const Hit &b) { return a.key < b.key; };
     if (!std::is_sorted(hits.begin(), hits.end(), by_key)) std::sort(hits.begin(), hits.end(), by_key);
     if (max_hits && hits.size() > max_hits) hits.resize(max_hits);
+    mark("done");
     return true;
 }
 

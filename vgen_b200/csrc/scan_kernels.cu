@@ -4,6 +4,7 @@
 // (src/shaders/search.wgsl:2-152) and their dispatch code (src/gpu.rs:502-518,535-600).
 #include <cuda_runtime.h>
 #include "scan_core.cuh"
+#include "taproot.cuh"
 #include "kernels.h"
 
 namespace vg {
@@ -50,17 +51,17 @@ __global__ void k_build_gtab(uint32_t *gtab, uint32_t half, const uint32_t *pow2
 
 // tab[j][v][16] = (v << (bits*j)) * G for the P2TR tweak addition; v = 0 entries are never read (all-zero)
 __global__ void k_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2) {
-    const unsigned long long n = (256ull / bits) << bits;
+    const unsigned long long n = (unsigned long long)vg_tap_windows(bits) << bits;
     unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1ull << bits) - 1));
-    uint32_t k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    uint32_t bit = j * bits;
-    k[bit >> 5] = v << (bit & 31u);                 // bits divides 32: a digit never straddles a limb
+    uint32_t k[8];
     fe x, y;
-    bool ok = v != 0 && scalar_mul_pow2(x, y, k, pow2);
+    bool ok = vg_tap_digit_scalar(k, j, v, bits) && scalar_mul_pow2(x, y, k, pow2);
     if (!ok) { fe_set_zero(x); fe_set_zero(y); }
-    for (int l = 0; l < 8; l++) { tab[i * 16 + l] = x.v[l]; tab[i * 16 + 8 + l] = y.v[l]; }
+    uint4 *o = (uint4 *)(tab + i * 16);
+    o[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]); o[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
+    o[2] = make_uint4(y.v[0], y.v[1], y.v[2], y.v[3]); o[3] = make_uint4(y.v[4], y.v[5], y.v[6], y.v[7]);
 }
 
 // P2TR internal keys as the reference's dispatch_p2tr / await_result_p2tr return them (src/gpu.rs:667-807): the
@@ -85,7 +86,7 @@ cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, c
     return cudaGetLastError();
 }
 cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2, cudaStream_t s) {
-    const unsigned long long n = (256ull / bits) << bits;
+    const unsigned long long n = (unsigned long long)((256u + bits - 1u) / bits) << bits;
     k_build_tap_table<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(tab, bits, pow2);
     return cudaGetLastError();
 }

@@ -9,7 +9,7 @@
 //   stage 2 (this file): t = SHA256(SHA256("TapTweak") || SHA256("TapTweak") || x)   [one compression from a
 //           precomputed midstate, same constant as src/shaders/sha256.wgsl:177-249]
 //           Q = P + t*G through a fixed-base table tab[j][v] = v * 2^(bits*j) * G (bits = 16: 16 mixed additions,
-//           64 MiB, L2-resident), kept in Jacobian form; one field inversion per VG_TAP_GROUP keys (Montgomery's
+//           64 MiB, L2-resident; bits = 24: 11 additions, 11 GiB of HBM gathered at random), kept in Jacobian form; one field inversion per VG_TAP_GROUP keys (Montgomery's
 //           trick over the group's Z^2) turns X/Z^2 into the 32-byte witness program x(Q), which goes through the
 //           same matcher as the other formats (interval / exact / Bech32m-fed DFA).
 #pragma once
@@ -57,6 +57,27 @@ VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
     return true;
 }
 
+// Fixed-base table geometry: ceil(256 / bits) windows of 2^bits entries; window j, digit v holds (v * 2^(bits*j)) * G.
+// `bits` need not divide 32 or 256 (24-bit windows: 11 windows, the top one uses 16 bits).
+VG_DEV uint32_t vg_tap_windows(uint32_t bits) { return (256u + bits - 1u) / bits; }
+// k = v * 2^(bits*j) as 8 little-endian limbs; false when v is 0 or the product does not fit in 256 bits (unused entry)
+VG_DEV bool vg_tap_digit_scalar(uint32_t k[8], uint32_t j, uint32_t v, uint32_t bits) {
+    const uint32_t bit = j * bits, wi = bit >> 5, sh = bit & 31u;
+    for (int i = 0; i < 8; i++) k[i] = 0;
+    if (v == 0 || bit >= 256u) return false;
+    if (bit + bits > 256u && (v >> (256u - bit)) != 0) return false;
+    k[wi] = v << sh;
+    if (sh != 0 && wi + 1 < 8) k[wi + 1] = v >> (32u - sh);
+    return true;
+}
+// digit j of t (t as 8 big-endian words: word 7 is the least significant)
+VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t j, uint32_t bits) {
+    const uint32_t bit = j * bits, wi = bit >> 5, sh = bit & 31u, mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
+    uint32_t lo = 0, hi = 0;
+    VG_UNROLL for (int i = 0; i < 8; i++) { lo = (wi == (uint32_t)i) ? t[7 - i] : lo; hi = (wi + 1u == (uint32_t)i) ? t[7 - i] : hi; }
+    return (sh ? ((lo >> sh) | (hi << (32u - sh))) : lo) & mask;
+}
+
 // Q = P + t*G in Jacobian coordinates. Returns false when Q is the point at infinity (t*G = -P).
 // FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false).
 // FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
@@ -64,7 +85,7 @@ template <bool FAST>
 VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true) {
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
     bool special = false;
-    const uint32_t n_win = 256u / bits, mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
+    const uint32_t n_win = vg_tap_windows(bits), mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
 #ifndef VG_HOST_EMU
     #pragma unroll 1
 #endif
@@ -72,11 +93,7 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
 #if VG_TAP_SYNC >= 2 && !defined(VG_HOST_EMU)
         if (FAST) __syncthreads();      // every thread of the CTA runs all n_win iterations (inactive ones skip the addition)
 #endif
-        const uint32_t bit = j * bits;
-        // bit position counted from the least significant end of t; word 7 is the least significant
-        uint32_t word = 0;
-        VG_UNROLL for (int i = 0; i < 8; i++) word = ((bit >> 5) == (uint32_t)i) ? t[7 - i] : word;
-        const uint32_t v = (word >> (bit & 31u)) & mask;
+        const uint32_t v = vg_tap_digit(t, j, bits);
         if (v == 0 || !active || special) continue;
         const uint32_t *e = tab + ((size_t)j * ((size_t)mask + 1) + v) * 16;
         fe bx, by;
