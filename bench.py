@@ -24,9 +24,13 @@ METRIC = "Mkeys/s P2PKH ^1Cat scan"
 START = 1 << 64
 # algorithmic work per key, 32-bit integer instruction slots (DESIGN.md "Roofline"; SURVEY.md 8d, +/- variant, c_w = 1):
 #   EC 3.5M + 1S = 300.5 limb products + ~300 carry/add slots, SHA-256 ~1400, RIPEMD-160 ~975, matcher ~15
-W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed": 4450, "ethereum": 5220,
-         # P2TR: walk 4.5 field mults + tweak stage 16 x (8M + 3S) + 4 + 270/16 = ~201.5 mults x ~147 slots, + one SHA-256 compression
-         "p2tr": 31000}
+W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed": 4450,
+         # Ethereum: Keccak-f[1600] on 32-bit halves = 24 x (122 LOP3 + 58 SHF) = 4,320 + walk (both coordinates) ~1,080;
+         # ncu counts 5,509 executed per key (profiles/ncu_walk_eth_r01_summary.txt)
+         "ethereum": 5400,
+         # P2TR: walk 4.5 field mults + tweak stage A x (8M + 3S) + 4 + 270/16 mults x ~147 slots + one SHA-256 compression,
+         # A = 10 additions with the 26-bit table bench_resident builds (long-job setting; 24 bits: 11, ~22,900; 16 bits: 16, ~31,000)
+         "p2tr": 21300}
 HBM_BYTES_PER_KEY = 32          # prefix-product scratch: 32 B written + 32 B read per +/- key pair
 
 
@@ -136,7 +140,11 @@ def run_reference(args):
 
 
 def workload_config(args, runner):
-    cfg = {"workload": "BASELINE configs[1] shape: P2PKH compressed prefix scan (hash160 interval-compare path), pattern %s, fixed key range from 2^64" % args.pattern,
+    if args.format == "p2pkh" and args.pattern == "^1Cat":
+        what = "BASELINE configs[1] shape: P2PKH compressed prefix scan (hash160 interval-compare path), pattern ^1Cat, fixed key range from 2^64"
+    else:
+        what = "%s scan, pattern %s, fixed key range from 2^64 (not the headline workload)" % (args.format, args.pattern)
+    cfg = {"workload": what,
            "format": args.format, "pattern": args.pattern, "start": "2^64", "windows_per_step": args.windows_per_step,
            "parallelism": "keyspace shards, %d rank(s), no collective; 2 overlapping streams per GPU" % args.gpus,
            "l2": "per-launch working set (prefix-product scratch, 1.24 GB) exceeds the 126 MB L2; no flush needed"}

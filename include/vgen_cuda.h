@@ -111,6 +111,9 @@ uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx);
 /* lanes of the context: every GPU is driven through 2 streams (each with its own centres, scratch and hit buffers) whose
  * windows overlap, so that a window's late warps do not leave the SMs under-occupied; lanes = 2 x GPUs */
 int vgen_cuda_lane_count(const vgen_ctx *ctx);
+/* window width (bits) of the P2TR fixed-base table this context has built: 0 none yet, 16 for short jobs, 24 for jobs of
+ * at least 2^30 keys, 26 from 2^36 keys (or what VGEN_TAP_BITS forces); a wider table is kept once built */
+int vgen_cuda_tap_bits(const vgen_ctx *ctx);
 /* bytes the scans of this context copied host->device (start scalars, launch parameters) and device->host (counters, hit records) */
 void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h);
 

@@ -168,6 +168,24 @@ def test_p2tr_exact_address_planted(small_runner):
     assert small_runner.matcher_kind() == "exact"
 
 
+def test_p2tr_long_job_builds_the_wide_table(runner):
+    """A P2TR job of at least 2^32 keys switches the tweak stage to the 24-bit fixed-base table (11 GiB in HBM, 11 additions
+    per key instead of 16; engine.cpp ensure_taproot). Same results as the oracle, through the scan and the digest path."""
+    import os
+    start, n = 2**70, (1 << 32) + 12345
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2tr, count=5, start=start, end=start + n - 1)
+    res = vg.scan_gpu_with_runner(vg.Pattern("^bc1pqq"), cfg, None, None, runner)
+    if "VGEN_TAP_BITS" not in os.environ:
+        assert runner.tap_bits() == 24
+    keys, _, _ = oracle.scan_range("p2tr", "^bc1pqq", start, 30000)
+    assert len(keys) >= 5 and [int(m.hex, 16) for m in res.matches] == keys[:5]
+    for m in res.matches:
+        assert m.address == oracle.address("p2tr", int(m.hex, 16))[0]
+    got = runner.digest_batch("p2tr", start + 777, 3000)          # the wide table stays in place for short calls
+    assert got == oracle.digest_batch("p2tr", start + 777, 3000)
+    assert "VGEN_TAP_BITS" in os.environ or runner.tap_bits() == 24
+
+
 def test_config_c1_full_match_set(runner):
     """BASELINE.json config C1: 2^24-key window from 2^64, P2PKH, ^1Cat — full match set vs the oracle."""
     res = _check_scan(runner, "p2pkh", "^1Cat", 2**64, 1 << 24)

@@ -1,13 +1,12 @@
 #!/bin/bash
-# One GPU-box pass: full GPU test suite, default bench + reference arm, full-size C2 (incl. the alternation pattern),
-# P2TR bench and a fresh ncu capture of the tweak stage. Outputs under gpurun_out/.
+# One GPU-box pass: full GPU test suite, default bench, Ethereum (32-bit-halves Keccak) and P2TR (auto table width) benches,
+# ncu capture of the Ethereum walk kernel. Outputs under gpurun_out/.
 set -u
 O=gpurun_out
-timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > $O/pytest_h.log
-timeout 300 python bench.py > $O/bench_h.json 2> $O/bench_h.err
-timeout 200 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_h_ref.json 2> $O/bench_h_ref.err
-timeout 300 python tests/full_size_configs.py c2 > $O/full_c2_h.log 2>&1
-timeout 300 python bench.py --steps 3 --warmup 3 --windows-per-step 4 --format p2tr --pattern '^bc1pcat' --no-cpu-baseline > $O/bench_h_p2tr.json 2> $O/bench_h_p2tr.err
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_taptweak -c 1 -o $O/ncu_taptweak_h -f python bench.py --steps 1 --warmup 3 --windows-per-step 1 --format p2tr --pattern '^bc1pcat' --no-cpu-baseline > $O/ncu_tap_h.log 2>&1
-timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_p2tr_h.csv python bench.py --steps 1 --warmup 3 --windows-per-step 2 --format p2tr --pattern '^bc1pcat' --no-cpu-baseline > $O/ncu_tap_l_h.log 2>&1
+timeout 1200 python -m pytest tests -m gpu -x -q 2>&1 | tail -15 > $O/pytest_j.log
+timeout 300 python bench.py > $O/bench_j.json 2> $O/bench_j.err
+timeout 300 python bench.py --steps 4 --warmup 3 --windows-per-step 8 --format ethereum --pattern '^0xdead' --no-cpu-baseline > $O/bench_j_eth.json 2> $O/bench_j_eth.err
+timeout 300 python bench.py --steps 4 --warmup 3 --windows-per-step 8 --format ethereum --pattern 'F00$' --no-cpu-baseline > $O/bench_j_eth_dfa.json 2> $O/bench_j_eth_dfa.err
+VGEN_TRACE=1 timeout 300 python bench.py --steps 3 --warmup 3 --windows-per-step 4 --format p2tr --pattern '^bc1pcat' --no-cpu-baseline > $O/bench_j_p2tr.json 2> $O/bench_j_p2tr.err
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_walk -c 1 -o $O/ncu_walk_eth_b -f python bench.py --steps 1 --warmup 3 --windows-per-step 1 --format ethereum --pattern '^0xdead' --no-cpu-baseline > $O/ncu_eth_b.log 2>&1
 echo done

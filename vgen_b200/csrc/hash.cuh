@@ -286,61 +286,91 @@ VG_CONST uint64_t VG_KECCAK_RC[24] = {
     0x8000000000008002ULL,0x8000000000000080ULL,0x000000000000800aULL,0x800000008000000aULL,
     0x8000000080008081ULL,0x8000000000008080ULL,0x0000000080000001ULL,0x8000000080008008ULL};
 
-VG_DEV uint64_t vg_rotl64(uint64_t x, int n) { return (x << n) | (x >> (64 - n)); }
+// 64-bit lanes are kept as two 32-bit halves (L = low, H = high) so that every rotation half is exactly one funnel
+// shift (SHF) and every xor / chi one LOP3. Written on uint64_t, nvcc lowers part of the rotations to shift + shift + or
+// and rotl-by-1 to add-with-carry: 248 instructions per round against 180 here (ncu: 7,021 -> see DESIGN.md).
+template <int N> VG_DEV void vg_rotl64_halves(uint32_t &ol, uint32_t &oh, uint32_t l, uint32_t h) {
+    if (N == 0) { ol = l; oh = h; }
+    else if (N < 32) { oh = vg_shf_l(l, h, N & 31); ol = vg_shf_l(h, l, N & 31); }
+    else if (N == 32) { ol = h; oh = l; }
+    else { oh = vg_shf_l(h, l, (N - 32) & 31); ol = vg_shf_l(l, h, (N - 32) & 31); }
+}
+VG_DEV uint32_t vg_xor3(uint32_t a, uint32_t b, uint32_t c) {
+#ifdef VG_HOST_EMU
+    return a ^ b ^ c;
+#else
+    uint32_t r;
+    asm("lop3.b32 %0,%1,%2,%3,0x96;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+#endif
+}
+// b[DST] = rotl64(s[SRC] ^ d[SRC % 5], N), with d[x] = c[x-1] ^ rotl64(c[x+1], 1) folded into a 3-input xor
+#define VG_K_RHO(DST, SRC, N) vg_rotl64_halves<N>(bl[DST], bh[DST], vg_xor3(sl[SRC], ca_l[(SRC) % 5], r1_l[(SRC) % 5]), vg_xor3(sh[SRC], ca_h[(SRC) % 5], r1_h[(SRC) % 5]))
 
 // VG_KECCAK_UNROLL: 1 = fully unrolled rounds (round-constant loads fold, the zero lanes of the first round and the
-// unused lanes of the last one are eliminated), 0 = rolled loop (smaller code). Measured on B200: unrolled is 9 % slower;
-// folding theta's D[x] into 3-input LOP3 lane updates by hand changes nothing (2,895 vs 2,897 Mkeys/s).
+// unused lanes of the last one are eliminated), 0 = rolled loop (smaller code). Measured on B200 (64-bit version):
+// unrolled is 9 % slower (instruction cache).
 #ifndef VG_KECCAK_UNROLL
 #define VG_KECCAK_UNROLL 0
 #endif
-VG_DEV void keccak_f1600(uint64_t s[25]) {
+VG_DEV void keccak_f1600(uint32_t sl[25], uint32_t sh[25]) {
 #if VG_KECCAK_UNROLL && !defined(VG_HOST_EMU)
     #pragma unroll
+#else
+  #ifndef VG_HOST_EMU
+    #pragma unroll 1
+  #endif
 #endif
     for (int r = 0; r < 24; r++) {
-        uint64_t c0 = s[0] ^ s[5] ^ s[10] ^ s[15] ^ s[20], c1 = s[1] ^ s[6] ^ s[11] ^ s[16] ^ s[21];
-        uint64_t c2 = s[2] ^ s[7] ^ s[12] ^ s[17] ^ s[22], c3 = s[3] ^ s[8] ^ s[13] ^ s[18] ^ s[23];
-        uint64_t c4 = s[4] ^ s[9] ^ s[14] ^ s[19] ^ s[24];
-        uint64_t d0 = c4 ^ vg_rotl64(c1, 1), d1 = c0 ^ vg_rotl64(c2, 1), d2 = c1 ^ vg_rotl64(c3, 1);
-        uint64_t d3 = c2 ^ vg_rotl64(c4, 1), d4 = c3 ^ vg_rotl64(c0, 1);
-        uint64_t b[25];
-        b[0] = s[0] ^ d0;
-        b[10] = vg_rotl64(s[1] ^ d1, 1);   b[20] = vg_rotl64(s[2] ^ d2, 62);  b[5] = vg_rotl64(s[3] ^ d3, 28);   b[15] = vg_rotl64(s[4] ^ d4, 27);
-        b[16] = vg_rotl64(s[5] ^ d0, 36);  b[1] = vg_rotl64(s[6] ^ d1, 44);   b[11] = vg_rotl64(s[7] ^ d2, 6);   b[21] = vg_rotl64(s[8] ^ d3, 55);
-        b[6] = vg_rotl64(s[9] ^ d4, 20);   b[7] = vg_rotl64(s[10] ^ d0, 3);   b[17] = vg_rotl64(s[11] ^ d1, 10); b[2] = vg_rotl64(s[12] ^ d2, 43);
-        b[12] = vg_rotl64(s[13] ^ d3, 25); b[22] = vg_rotl64(s[14] ^ d4, 39); b[23] = vg_rotl64(s[15] ^ d0, 41); b[8] = vg_rotl64(s[16] ^ d1, 45);
-        b[18] = vg_rotl64(s[17] ^ d2, 15); b[3] = vg_rotl64(s[18] ^ d3, 21);  b[13] = vg_rotl64(s[19] ^ d4, 8);  b[14] = vg_rotl64(s[20] ^ d0, 18);
-        b[24] = vg_rotl64(s[21] ^ d1, 2);  b[9] = vg_rotl64(s[22] ^ d2, 61);  b[19] = vg_rotl64(s[23] ^ d3, 56); b[4] = vg_rotl64(s[24] ^ d4, 14);
-        VG_UNROLL for (int j = 0; j < 25; j += 5) {
-            s[j + 0] = b[j + 0] ^ (~b[j + 1] & b[j + 2]); s[j + 1] = b[j + 1] ^ (~b[j + 2] & b[j + 3]);
-            s[j + 2] = b[j + 2] ^ (~b[j + 3] & b[j + 4]); s[j + 3] = b[j + 3] ^ (~b[j + 4] & b[j + 0]);
-            s[j + 4] = b[j + 4] ^ (~b[j + 0] & b[j + 1]);
+        uint32_t cl[5], ch[5];
+        VG_UNROLL for (int x = 0; x < 5; x++) {
+            cl[x] = vg_xor3(vg_xor3(sl[x], sl[x + 5], sl[x + 10]), sl[x + 15], sl[x + 20]);
+            ch[x] = vg_xor3(vg_xor3(sh[x], sh[x + 5], sh[x + 10]), sh[x + 15], sh[x + 20]);
         }
-        s[0] ^= VG_KECCAK_RC[r];
+        // for column x: ca = c[x-1], r1 = rotl64(c[x+1], 1)
+        uint32_t ca_l[5], ca_h[5], r1_l[5], r1_h[5];
+        VG_UNROLL for (int x = 0; x < 5; x++) {
+            ca_l[x] = cl[(x + 4) % 5]; ca_h[x] = ch[(x + 4) % 5];
+            vg_rotl64_halves<1>(r1_l[x], r1_h[x], cl[(x + 1) % 5], ch[(x + 1) % 5]);
+        }
+        uint32_t bl[25], bh[25];
+        VG_K_RHO(0, 0, 0);
+        VG_K_RHO(10, 1, 1);   VG_K_RHO(20, 2, 62);  VG_K_RHO(5, 3, 28);   VG_K_RHO(15, 4, 27);
+        VG_K_RHO(16, 5, 36);  VG_K_RHO(1, 6, 44);   VG_K_RHO(11, 7, 6);   VG_K_RHO(21, 8, 55);
+        VG_K_RHO(6, 9, 20);   VG_K_RHO(7, 10, 3);   VG_K_RHO(17, 11, 10); VG_K_RHO(2, 12, 43);
+        VG_K_RHO(12, 13, 25); VG_K_RHO(22, 14, 39); VG_K_RHO(23, 15, 41); VG_K_RHO(8, 16, 45);
+        VG_K_RHO(18, 17, 15); VG_K_RHO(3, 18, 21);  VG_K_RHO(13, 19, 8);  VG_K_RHO(14, 20, 18);
+        VG_K_RHO(24, 21, 2);  VG_K_RHO(9, 22, 61);  VG_K_RHO(19, 23, 56); VG_K_RHO(4, 24, 14);
+        VG_UNROLL for (int j = 0; j < 25; j += 5) {
+            VG_UNROLL for (int x = 0; x < 5; x++) {
+                sl[j + x] = bl[j + x] ^ (~bl[j + (x + 1) % 5] & bl[j + (x + 2) % 5]);
+                sh[j + x] = bh[j + x] ^ (~bh[j + (x + 1) % 5] & bh[j + (x + 2) % 5]);
+            }
+        }
+        sl[0] ^= (uint32_t)VG_KECCAK_RC[r];
+        sh[0] ^= (uint32_t)(VG_KECCAK_RC[r] >> 32);
     }
 }
 // Ethereum address words: Keccak-256(X || Y)[12..32] as 5 words, digest byte 4i+j = byte j of out[i]
 VG_DEV void keccak_eth_address(uint32_t out[5], const fe &x, const fe &y) {
-    uint64_t s[25];
-    VG_UNROLL for (int i = 0; i < 4; i++) {
-        s[i] = (uint64_t)vg_bswap(x.v[7 - 2 * i]) | ((uint64_t)vg_bswap(x.v[6 - 2 * i]) << 32);
-        s[4 + i] = (uint64_t)vg_bswap(y.v[7 - 2 * i]) | ((uint64_t)vg_bswap(y.v[6 - 2 * i]) << 32);
+    uint32_t sl[25], sh[25];
+    VG_UNROLL for (int i = 0; i < 4; i++) {      // lane i = message bytes 8i..8i+7, little-endian
+        sl[i] = vg_bswap(x.v[7 - 2 * i]);     sh[i] = vg_bswap(x.v[6 - 2 * i]);
+        sl[4 + i] = vg_bswap(y.v[7 - 2 * i]); sh[4 + i] = vg_bswap(y.v[6 - 2 * i]);
     }
-    s[8] = 0x01ULL;
-    VG_UNROLL for (int i = 9; i < 25; i++) s[i] = 0;
-    s[16] = 0x8000000000000000ULL;
-    keccak_f1600(s);
-    out[0] = (uint32_t)(s[1] >> 32); out[1] = (uint32_t)s[2]; out[2] = (uint32_t)(s[2] >> 32);
-    out[3] = (uint32_t)s[3]; out[4] = (uint32_t)(s[3] >> 32);
+    VG_UNROLL for (int i = 8; i < 25; i++) { sl[i] = 0; sh[i] = 0; }
+    sl[8] = 0x01u;
+    sh[16] = 0x80000000u;
+    keccak_f1600(sl, sh);
+    out[0] = sh[1]; out[1] = sl[2]; out[2] = sh[2]; out[3] = sl[3]; out[4] = sh[3];
 }
 // Keccak-256 of 40 ASCII bytes (the lowercase hex of an address) -> first 20 digest bytes as 5 LE words
 VG_DEV void keccak_hex40(uint32_t out[5], const uint32_t m[10]) {   // m: message bytes as little-endian words
-    uint64_t s[25];
-    VG_UNROLL for (int i = 0; i < 5; i++) s[i] = (uint64_t)m[2 * i] | ((uint64_t)m[2 * i + 1] << 32);
-    s[5] = 0x01ULL;
-    VG_UNROLL for (int i = 6; i < 25; i++) s[i] = 0;
-    s[16] = 0x8000000000000000ULL;
-    keccak_f1600(s);
-    out[0] = (uint32_t)s[0]; out[1] = (uint32_t)(s[0] >> 32); out[2] = (uint32_t)s[1]; out[3] = (uint32_t)(s[1] >> 32); out[4] = (uint32_t)s[2];
+    uint32_t sl[25], sh[25];
+    VG_UNROLL for (int i = 0; i < 5; i++) { sl[i] = m[2 * i]; sh[i] = m[2 * i + 1]; }
+    VG_UNROLL for (int i = 5; i < 25; i++) { sl[i] = 0; sh[i] = 0; }
+    sl[5] = 0x01u;
+    sh[16] = 0x80000000u;
+    keccak_f1600(sl, sh);
+    out[0] = sl[0]; out[1] = sh[0]; out[2] = sl[1]; out[3] = sh[1]; out[4] = sl[2];
 }

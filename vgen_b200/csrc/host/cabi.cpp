@@ -182,6 +182,7 @@ void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h) {
     if (d2h) *d2h = ctx ? ctx->engine.d2h_bytes : 0;
 }
 int vgen_cuda_lane_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.n_lanes() : 0; }
+int vgen_cuda_tap_bits(const vgen_ctx *ctx) { return ctx ? (int)ctx->engine.tap_bits() : 0; }
 uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx) { return ctx ? ctx->engine.levels().back().window : 0; }
 
 int vgen_format_address(int format, const uint8_t *digest, char *out, size_t cap) {

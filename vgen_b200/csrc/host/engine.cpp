@@ -132,32 +132,60 @@ bool Engine::upload_dfa(std::string &err) {
     return true;
 }
 
-// Window width of the P2TR fixed-base table. 16: 16 windows x 65,536 x 64 B = 64 MiB, resident in the 126 MB L2.
-// VGEN_TAP_BITS overrides (4..26; 24 = 11 windows x 16 Mi x 64 B = 11 GiB gathered from HBM, 5 additions fewer per key).
-static uint32_t tap_bits_from_env() {
-    const char *e = getenv("VGEN_TAP_BITS");
-    long v = e ? strtol(e, nullptr, 10) : 16;
-    return (uint32_t)(v < 4 ? 4 : v > 26 ? 26 : v);
+// Window width of the P2TR fixed-base table (taproot.cuh), chosen per job (measured on B200, profiles/tap_bits_r01.log):
+//   16 bits: 16 windows x 65,536 x 64 B = 64 MiB, built in 2 ms; 16 additions per key                      476 Mkeys/s
+//   24 bits: 11 windows x 2^24 x 64 B = 11 GiB of the 180 GB HBM, built in 0.15 s; 11 additions per key     638 Mkeys/s
+//   26 bits: 10 windows x 2^26 x 64 B = 40 GiB, built in 0.43 s; 10 additions per key                       683 Mkeys/s
+// The entries are gathered at random from DRAM either way (ncu: the 64 MiB table is flushed out of L2 by the window's point
+// stream), so a wider table only saves additions. Jobs of >= 2^30 keys take 24 bits, >= 2^36 keys 26 bits (when the
+// device has the room). VGEN_TAP_BITS (4..26) forces a width.
+static uint32_t tap_bits_for(uint64_t keys_hint) {
+    static const char *e = getenv("VGEN_TAP_BITS");
+    if (e) { long v = strtol(e, nullptr, 10); return (uint32_t)(v < 4 ? 4 : v > 26 ? 26 : v); }
+    return keys_hint >= (1ull << 36) ? 26u : keys_hint >= (1ull << 30) ? 24u : 16u;
 }
-static const uint32_t kTapBits = tap_bits_from_env();
 static size_t tap_table_bytes(uint32_t bits) { return ((size_t)((256 + bits - 1) / bits) << bits) * 64; }
 
 // P2TR needs two more buffers per lane: the stage-1 -> stage-2 point buffer (64 B per window key) and the
-// fixed-base table of the tweak addition. Allocated and built on first use.
-bool Engine::ensure_taproot(std::string &err) {
+// fixed-base table of the tweak addition (one per GPU, shared by its lanes). Allocated and built on first use; a
+// wider table replaces a narrower one when a big job comes, never the other way round.
+bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
     const Level &F = levels_.back();
+    uint32_t want = tap_bits_for(keys_hint);
     for (auto &L : lanes_) {
-        if (L.d_tap_table) continue;
+        if (L.d_points) continue;
         CK(cudaSetDevice(L.device));
         CK(cudaMalloc(&L.d_points, (size_t)F.window * 64));
-        for (auto &O : lanes_) if (&O != &L && O.device == L.device && O.d_tap_table) L.d_tap_table = O.d_tap_table;   // one table per GPU
-        if (L.d_tap_table) continue;
-        CK(cudaMalloc(&L.d_tap_table, tap_table_bytes(kTapBits)));
-        L.owns_tap_table = true;
-        CK(launch_build_tap_table(L.d_tap_table, kTapBits, L.d_pow2, L.stream));
-        launches++;
-        CK(cudaStreamSynchronize(L.stream));
     }
+    if (tap_bits_ != 0 && (tap_bits_ >= want || getenv("VGEN_TAP_BITS"))) return true;
+    for (auto &L : lanes_) {            // a big table needs room: fall back to the small one on a crowded device
+        size_t free_b = 0, total_b = 0;
+        CK(cudaSetDevice(L.device));
+        CK(cudaMemGetInfo(&free_b, &total_b));
+        const size_t held = tap_bits_ ? tap_table_bytes(tap_bits_) : 0;      // freed before the new one is allocated
+        if (want > 24 && free_b + held < tap_table_bytes(want) + (8ull << 30)) want = 24;
+        if (want > 16 && free_b + held < tap_table_bytes(want) + (4ull << 30)) want = 16;
+    }
+    if (tap_bits_ >= want && tap_bits_ != 0) return true;
+    const auto t0 = std::chrono::steady_clock::now();
+    for (auto &L : lanes_) { CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); }
+    for (auto &L : lanes_) {
+        if (L.owns_tap_table && L.d_tap_table) { CK(cudaSetDevice(L.device)); CK(cudaFree(L.d_tap_table)); }
+        L.d_tap_table = nullptr; L.owns_tap_table = false;
+    }
+    for (auto &L : lanes_) {
+        for (auto &O : lanes_) if (&O != &L && O.device == L.device && O.d_tap_table) L.d_tap_table = O.d_tap_table;
+        if (L.d_tap_table) continue;
+        CK(cudaSetDevice(L.device));
+        CK(cudaMalloc(&L.d_tap_table, tap_table_bytes(want)));
+        L.owns_tap_table = true;
+        CK(launch_build_tap_table(L.d_tap_table, want, L.d_pow2, L.stream));
+        launches++;
+    }
+    for (auto &L : lanes_) { CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); }
+    tap_bits_ = want;
+    if (getenv("VGEN_TRACE"))
+        fprintf(stderr, "[vgen trace] tap table %u bits     %9.3f ms\n", want, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     return true;
 }
 
@@ -166,7 +194,6 @@ bool Engine::set_pattern(int format, const std::string &pattern, bool ci, std::s
     if (!lower_pattern(format, pattern, ci, lp, err)) return false;
     lp_ = lp;
     has_pattern_ = true;
-    if (format == VG_FMT_P2TR && !ensure_taproot(err)) return false;
     return upload_dfa(err);
 }
 
@@ -213,7 +240,7 @@ void Engine::fill_params(Lane &L, Slot &S, vg_scan_params &P) {
     P.limit = S.limit;
     P.hits = S.d_hits; P.hit_count = S.d_counters; P.hit_cap = (uint32_t)std::min<uint64_t>(V.window, 0xffffffffu);
     P.degen_list = S.d_degen; P.degen_count = S.d_counters + 1; P.degen_cap = V.threads;
-    P.points = L.d_points; P.tap_table = L.d_tap_table; P.tap_bits = kTapBits;
+    P.points = L.d_points; P.tap_table = L.d_tap_table; P.tap_bits = tap_bits_;
     P.m = lp_.dev;
     P.m.dfa.table = L.d_dfa_table; P.m.dfa.accept = L.d_dfa_accept;
     P.dfa_smem_bytes = (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa) ? dfa_smem_bytes(P.m.dfa) : 0;
@@ -264,6 +291,7 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
         return true;
     }
     const U256 N = end.sub(start).add64(1);            // >= 1; cannot wrap because end <= n-1 < 2^256-1
+    if (lp_.format == VG_FMT_P2TR && !ensure_taproot(N.fits64() ? N.w[0] : ~0ULL, err)) return false;
     // VGEN_TRACE=1: phase timestamps of this call on stderr (ms since entry)
     static const bool trace = getenv("VGEN_TRACE") != nullptr;
     const auto t_entry = std::chrono::steady_clock::now();
@@ -436,7 +464,7 @@ bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *ou
         U256 room = secp_order_minus1().sub(start).add64(1);
         if (room.fits64() && room.w[0] < n) n = room.w[0];
     }
-    if (format == VG_FMT_P2TR && !ensure_taproot(err)) return false;
+    if (format == VG_FMT_P2TR && !ensure_taproot(n, err)) return false;
     Lane &L = lanes_[0];
     CK(cudaSetDevice(L.device));
     uint32_t saved_idx = shard_index_, saved_cnt = shard_count_;
@@ -493,6 +521,7 @@ bool Engine::digest_batch(int format, const U256 &start, uint64_t n, uint8_t *ou
 
 bool Engine::bench_resident(const U256 &start, uint32_t n_windows, float &ms, uint64_t &keys, uint64_t &nlaunch, std::string &err) {
     if (!has_pattern_) { err = "no pattern set"; return false; }
+    if (lp_.format == VG_FMT_P2TR && !ensure_taproot(~0ULL, err)) return false;      // sustained rate: the long-job table
     if (!compute_stride_points(err)) return false;
     // the lanes of the first device, exactly as a scan drives them: window k of the sequence goes to lane k mod G
     std::vector<Lane *> ls;

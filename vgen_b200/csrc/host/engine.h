@@ -66,6 +66,7 @@ public:
     bool has_pattern() const { return has_pattern_; }
     static int lanes_per_device();      // lanes (streams) the engine opens on every GPU (default 2, VGEN_LANES_PER_GPU)
     int n_lanes() const { return (int)lanes_.size(); }
+    uint32_t tap_bits() const { return tap_bits_; }
     const Lane &lane(int i) const { return lanes_[i]; }
     uint32_t half() const { return half_; }
     const std::vector<Level> &levels() const { return levels_; }
@@ -77,7 +78,8 @@ private:
     bool launch_window(Lane &L, int s, int fmt, int mode, uint8_t *dump, uint32_t dump_stride, std::string &err);
     void fill_params(Lane &L, Slot &S, vg_scan_params &P);
     bool upload_dfa(std::string &err);
-    bool ensure_taproot(std::string &err);
+    bool ensure_taproot(uint64_t keys_hint, std::string &err);
+    uint32_t tap_bits_ = 0;                      // window width of the P2TR table currently built (0 = none)
     void destroy();
     std::vector<Lane> lanes_;
     std::vector<Level> levels_;

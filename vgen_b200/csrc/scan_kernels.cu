@@ -49,19 +49,63 @@ __global__ void k_build_gtab(uint32_t *gtab, uint32_t half, const uint32_t *pow2
     for (int l = 0; l < 8; l++) { gtab[i * 16 + l] = x.v[l]; gtab[i * 16 + 8 + l] = y.v[l]; }
 }
 
-// tab[j][v][16] = (v << (bits*j)) * G for the P2TR tweak addition; v = 0 entries are never read (all-zero)
-__global__ void k_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2) {
+// tab[j][v][16] = (v << (bits*j)) * G for the P2TR tweak addition; v = 0 entries are never read (all-zero).
+// One thread builds VG_TAPB_GROUP consecutive digits of one window: the first by 8-bit windowed multiplication kept in
+// Jacobian form, the others by adding B = 2^(bits*j) * G, and one field inversion turns the group into affine points
+// (the 24-bit table has 1.8e8 entries: an inversion per entry made its build 2.4 s). Digits of a partial top window that
+// would overflow 2^256 are never read; they are filled with whatever the addition chain gives.
+#define VG_TAPB_GROUP 16
+__global__ void k_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *gtable) {
     const unsigned long long n = (unsigned long long)vg_tap_windows(bits) << bits;
-    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1ull << bits) - 1));
-    uint32_t k[8];
-    fe x, y;
-    bool ok = vg_tap_digit_scalar(k, j, v, bits) && scalar_mul_pow2(x, y, k, pow2);
-    if (!ok) { fe_set_zero(x); fe_set_zero(y); }
-    uint4 *o = (uint4 *)(tab + i * 16);
-    o[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]); o[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
-    o[2] = make_uint4(y.v[0], y.v[1], y.v[2], y.v[3]); o[3] = make_uint4(y.v[4], y.v[5], y.v[6], y.v[7]);
+    const unsigned long long i0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * VG_TAPB_GROUP;
+    if (i0 >= n) return;
+    const uint32_t j = (uint32_t)(i0 >> bits), v0 = (uint32_t)(i0 & ((1ull << bits) - 1));
+    const uint32_t bit = j * bits, wi = bit >> 5, sh = bit & 31u;      // bit < 256
+    uint32_t k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    k[wi] = v0 << sh;
+    if (sh != 0 && wi + 1 < 8) k[wi + 1] = v0 >> (32u - sh);
+    fe Bx, By;
+    for (int l = 0; l < 8; l++) { Bx.v[l] = gtable[bit * 16 + l]; By.v[l] = gtable[bit * 16 + 8 + l]; }
+    // acc = k * G, Jacobian
+    const uint32_t *win8 = gtable + VG_GTABLE_POW2_WORDS;
+    gej_t acc; acc.inf = true;
+    fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
+    for (int b = 0; b < 32; b++) {
+        const uint32_t d = (k[b >> 2] >> (8 * (b & 3))) & 0xffu;
+        if (!d) continue;
+        const uint32_t *e = win8 + ((size_t)b * 256 + d) * 16;
+        fe ex, ey;
+        for (int l = 0; l < 8; l++) { ex.v[l] = e[l]; ey.v[l] = e[8 + l]; }
+        gej_t nr; gej_add_affine(nr, acc, ex, ey); acc = nr;
+    }
+    gej_t P[VG_TAPB_GROUP];
+    fe pre[VG_TAPB_GROUP];
+    fe run; fe_set_one(run);
+    #pragma unroll 1
+    for (int g = 0; g < VG_TAPB_GROUP; g++) {
+        P[g] = acc;
+        if (!acc.inf) fe_mul(run, run, acc.z);
+        pre[g] = run;
+        gej_t nr; gej_add_affine(nr, acc, Bx, By); acc = nr;
+    }
+    fe inv; fe_inv(inv, run);
+    #pragma unroll 1
+    for (int g = VG_TAPB_GROUP - 1; g >= 0; g--) {
+        fe x, y;
+        if (P[g].inf) { fe_set_zero(x); fe_set_zero(y); }
+        else {
+            fe zi, zi2, zi3;
+            if (g > 0) { fe_mul(zi, inv, pre[g - 1]); fe_mul(inv, inv, P[g].z); } else zi = inv;
+            fe_sqr(zi2, zi); fe_mul(zi3, zi2, zi);
+            fe_mul(x, P[g].x, zi2); fe_mul(y, P[g].y, zi3);
+            fe_canon(x); fe_canon(y);
+        }
+        if (i0 + g < n) {
+            uint4 *o = (uint4 *)(tab + (i0 + g) * 16);
+            o[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]); o[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
+            o[2] = make_uint4(y.v[0], y.v[1], y.v[2], y.v[3]); o[3] = make_uint4(y.v[4], y.v[5], y.v[6], y.v[7]);
+        }
+    }
 }
 
 // P2TR internal keys as the reference's dispatch_p2tr / await_result_p2tr return them (src/gpu.rs:667-807): the
@@ -87,7 +131,8 @@ cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, c
 }
 cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2, cudaStream_t s) {
     const unsigned long long n = (unsigned long long)((256u + bits - 1u) / bits) << bits;
-    k_build_tap_table<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(tab, bits, pow2);
+    const unsigned long long threads = (n + VG_TAPB_GROUP - 1) / VG_TAPB_GROUP;
+    k_build_tap_table<<<(unsigned)((threads + 127) / 128), 128, 0, s>>>(tab, bits, pow2);      // pow2: the full generator table (pow2 + win8)
     return cudaGetLastError();
 }
 cudaError_t launch_dump_points_x(const vg_scan_params &P, cudaStream_t s) {

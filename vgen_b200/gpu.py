@@ -159,6 +159,10 @@ class GpuRunner:
     def lane_count(self):
         return int(self._lib.vgen_cuda_lane_count(self._ctx))
 
+    def tap_bits(self):
+        """Window width of the P2TR fixed-base table built so far (0, 16 or 24; see include/vgen_cuda.h)."""
+        return int(self._lib.vgen_cuda_tap_bits(self._ctx))
+
     def launch_count(self):
         return int(self._lib.vgen_cuda_launch_count(self._ctx))
 
