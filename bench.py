@@ -28,9 +28,9 @@ W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed
          # Ethereum: Keccak-f[1600] on 32-bit halves = 24 x (122 LOP3 + 58 SHF) = 4,320 + walk (both coordinates) ~1,080;
          # ncu counts 5,509 executed per key (profiles/ncu_walk_eth_r01_summary.txt)
          "ethereum": 5400,
-         # P2TR: walk 4.5 field mults + tweak stage A x (8M + 3S) + 4 + 270/16 mults x ~147 slots + one SHA-256 compression,
-         # A = 10 additions with the 26-bit table bench_resident builds (long-job setting; 24 bits: 11, ~22,900; 16 bits: 16, ~31,000)
-         "p2tr": 21300}
+         # P2TR: walk 4.5 field mults + tweak stage A x (8M + 3S) + 4 + 270/64 mults x ~147 slots + one SHA-256 compression,
+         # A = 10 additions with the 26-bit table bench_resident builds (long-job setting; 24 bits: 11, ~21,000; 16 bits: 16, ~29,100)
+         "p2tr": 19400}
 HBM_BYTES_PER_KEY = 32          # prefix-product scratch: 32 B written + 32 B read per +/- key pair
 
 

@@ -59,6 +59,17 @@ int emu_confirm(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_
         case 3: return vg_confirm<3>(m, dv, dg); case 4: return vg_confirm<4>(m, dv, dg); default: return vg_confirm<5>(m, dv, dg);
     }
 }
+// Ethereum matcher with the case-folded DFA appended behind the exact one (lowering.cpp): table / accept hold both
+int emu_confirm_eth_fold(const uint32_t *dg, const uint16_t *table, const uint8_t *accept, const uint8_t *sym_class,
+                         uint32_t n_classes, uint32_t start, uint32_t flags, uint32_t fold_table, uint32_t fold_accept,
+                         uint32_t fold_classes, uint32_t fold_start, const uint8_t *fold_sym) {
+    vg_matcher_dev m; memset(&m, 0, sizeof m);
+    m.dfa.n_classes = n_classes; m.dfa.start = start; m.dfa.flags = flags;
+    m.dfa.fold_table = fold_table; m.dfa.fold_accept = fold_accept; m.dfa.fold_classes = fold_classes; m.dfa.fold_start = fold_start;
+    memcpy(m.dfa.fold_sym, fold_sym, 16);
+    vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
+    return vg_confirm<5>(m, dv, dg);
+}
 // P2TR stage 2 (taproot.cuh) over n keys (n a multiple of VG_TAP_GROUP) whose even-Y internal keys are in points[16*n]:
 // writes the 32-byte witness programs. bits = window width of the fixed-base table (4 keeps the host build cheap).
 static std::vector<uint32_t> g_tap; static uint32_t g_tap_bits = 0;

@@ -126,7 +126,7 @@ def test_walk_vs_oracle(emu, fmt, start, T, H, nw):
 def test_p2tr_two_stage_vs_oracle(emu):
     """taproot.cuh: stage 1 (walk -> even-Y internal keys) + stage 2 (TapTweak hash, t*G table addition, grouped
     inversion) must give the oracle's witness program (src/address.rs:136-140) for every key."""
-    T, H, nw = 2, 8, 2
+    T, H, nw = 4, 8, 2                      # window = 64 keys: a multiple of VG_TAP_GROUP
     total = T * 2 * H * nw
     for start in (1, 2**64 + 5, N - 2 * total - 100):
         out = C.create_string_buffer(32 * total)
@@ -138,7 +138,8 @@ def test_p2tr_two_stage_vs_oracle(emu):
 
 def test_p2tr_stage2_invalid_points_and_small_tweak_table(emu):
     # all-zero points (invalid scalar / outside the range) give all-zero programs; 8-bit windows agree with 4-bit ones
-    ks = [1, 2, 3, 0, 2**200 + 9, N - 1, 0, 77, 5, 0, 0, 2**255, 12345, N - 2, 0, 9]      # a multiple of VG_TAP_GROUP (16)
+    ks = [1, 2, 3, 0, 2**200 + 9, N - 1, 0, 77, 5, 0, 0, 2**255, 12345, N - 2, 0, 9]
+    ks = ks + [0, 0, 3**150, 2**128 - 1] + list(range(100, 112)) + ks[::-1] + [7**80 + i for i in range(16)]   # 64: a multiple of VG_TAP_GROUP
     pts = (C.c_uint32 * (16 * len(ks)))()
     for i, k in enumerate(ks):
         if k:
@@ -189,3 +190,27 @@ def test_device_matcher_vs_host_regex(emu, fmt, pats):
             want = oracle.regex_match(pat, addr)
             assert bool(got) == want, (fmt, pat, addr)
             n_hit += want
+
+
+def test_eth_folded_dfa_prefilter(emu):
+    """match.cuh vg_match_eth with the case-folded DFA appended (lowering.cpp): the prefilter on the lower-case hex must
+    never reject an address the case-sensitive pattern matches, and the combined verdict must equal the host regex."""
+    import vgen_b200 as vg
+    rng = random.Random(9)
+    F = vg.AddressFormat.Ethereum
+    emu.emu_confirm_eth_fold.restype = C.c_int
+    digests = [bytes(rng.randrange(256) for _ in range(20)) for _ in range(600)] + [b"\0" * 20, b"\xff" * 20, b"\xab" * 20]
+    digests += [bytes(rng.randrange(256) for _ in range(18)) + bytes([rng.randrange(16) * 16 + 15, 0]) for _ in range(80)]   # ...f00
+    for pat in ["F00$", "dEaD", "[A-F]{3}$", "aB", "^0xDe", "(?-i:Ab)", "^0x[a-f]", "c0FFee|Bad", "e$"]:
+        d, f = vg.Pattern(pat).device_dfa(F), vg.Pattern(pat.replace("(?-i:", "(?:"), True).device_dfa(F)
+        assert d["flags"] & 1 and not f["flags"] & 1
+        table, accept = d["table"] + f["table"], d["accept"] + f["accept"]
+        n_hit = 0
+        for dg in digests:
+            words = (C.c_uint32 * 8)(*[int.from_bytes(dg[4 * i:4 * i + 4], "little") if i < 5 else 0 for i in range(8)])
+            got = emu.emu_confirm_eth_fold(words, table, accept, d["sym_class"], d["n_classes"], d["start"], d["flags"],
+                                           len(d["table"]) // 2, len(d["accept"]), f["n_classes"], f["start"], f["sym_class"][:16])
+            want = oracle.regex_match(pat, oracle.address_from_digest("ethereum", dg))
+            assert bool(got) == want, (pat, dg.hex())
+            n_hit += want
+        assert pat not in ("F00$", "e$", "^0x[a-f]", "aB") or n_hit > 0, pat

@@ -121,6 +121,8 @@ def _check_scan(runner, fmt, pat, start, n, ci=False):
     # anchored alternations / optional tails: prefixes read off the DFA become digest intervals (lowering.cpp)
     ("p2pkh", "^(1Ca|1Do)", False), ("p2pkh", "^1(Ca|Do)t?x", False), ("p2wpkh", "^bc1q(aa|zz)", False),
     ("ethereum", "^0x(de|be)a", False), ("p2tr", "^bc1p(qq|pp)", False), ("p2sh-p2wpkh", "^(3Ab|3Cd)$", False),
+    # Ethereum case-sensitive patterns: the case-folded DFA runs first, the EIP-55 hash only for keys it accepts
+    ("ethereum", "[A-F]{3}$", False), ("ethereum", "(?-i:aB)", False), ("ethereum", "e$", False), ("ethereum", "Ab|cD", False),
 ])
 def test_scan_match_sets_small(small_runner, fmt, pat, ci):
     _check_scan(small_runner, fmt, pat, 2**64, 1 << 18, ci)

@@ -1,10 +1,11 @@
 #!/bin/bash
-# P2TR after the grouped table build: parity tests (16- and 24-bit tables), build times (VGEN_TRACE), widths 24 and 26.
+# P2TR inversion group A/B (32 = default build, 64 = variant), parity with the new default, P2PKH DFA-path rates.
 set -u
 O=gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q -k "p2tr or P2TR or taproot" 2>&1 | tail -5 > $O/pytest_tap_k.log
-VGEN_TAP_BITS=24 timeout 600 python -m pytest tests -m gpu -x -q -k "p2tr or P2TR or taproot" 2>&1 | tail -5 >> $O/pytest_tap_k.log
-for b in 16 24 26; do
-  VGEN_TRACE=1 VGEN_TAP_BITS=$b timeout 300 python bench.py --steps 3 --warmup 3 --windows-per-step 4 --format p2tr --pattern '^bc1pcat' --no-cpu-baseline > $O/tapbits_k_$b.json 2> $O/tapbits_k_$b.err
+timeout 900 python -m pytest tests -m gpu -x -q -k "p2tr or P2TR or taproot or match_sets" 2>&1 | tail -5 > $O/pytest_tap_m.log
+for v in "" _g64; do
+  VGEN_CUDA_LIB=$PWD/vgen_b200/libvgen_cuda$v.so timeout 300 python bench.py --steps 3 --warmup 3 --windows-per-step 4 --format p2tr --pattern '^bc1pcat' --no-cpu-baseline > $O/tapgroup_m$v.json 2> $O/tapgroup_m$v.err
 done
+timeout 300 python bench.py --steps 3 --warmup 3 --windows-per-step 8 --format p2pkh --pattern 'Cat$' --no-cpu-baseline > $O/bench_m_p2pkh_suffix.json 2> $O/bench_m_p2pkh_suffix.err
+timeout 300 python bench.py --steps 3 --warmup 3 --windows-per-step 8 --format p2pkh --pattern '(?i)satoshi' --no-cpu-baseline > $O/bench_m_p2pkh_sub.json 2> $O/bench_m_p2pkh_sub.err
 echo done

@@ -245,9 +245,11 @@ int vgen_pattern_dfa(int format, const char *pattern, int ci, uint16_t *table, s
     } catch (const std::exception &) { return VGEN_ERR_PATTERN; }
     info[0] = lp.dev.dfa.n_states; info[1] = lp.dev.dfa.n_classes; info[2] = lp.dev.dfa.start; info[3] = lp.dev.dfa.flags;
     if (sym_class) memcpy(sym_class, lp.dev.dfa.sym_class, 64);
-    if (!table || !accept || table_cap < lp.dfa.table.size() || accept_cap < lp.dfa.accept_end.size()) return VGEN_ERR_BUFFER;
-    memcpy(table, lp.dfa.table.data(), lp.dfa.table.size() * 2);
-    memcpy(accept, lp.dfa.accept_end.data(), lp.dfa.accept_end.size());
+    // the exact DFA only (an Ethereum case-folded prefilter DFA may be appended behind it, lowering.cpp)
+    const size_t tn = (size_t)lp.dfa.n_states * lp.dfa.n_classes, an = lp.dfa.n_states;
+    if (!table || !accept || table_cap < tn || accept_cap < an) return VGEN_ERR_BUFFER;
+    memcpy(table, lp.dfa.table.data(), tn * 2);
+    memcpy(accept, lp.dfa.accept_end.data(), an);
     return VGEN_OK;
 }
 int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, size_t cap) {

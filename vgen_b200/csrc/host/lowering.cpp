@@ -154,6 +154,7 @@ bool decode_exact(int format, const std::string &addr, uint8_t digest[32]) {
 void fill_device_dfa(int format, const Dfa &dfa, vg_dfa_dev &d) {
     memset(&d, 0, sizeof d);
     d.n_states = dfa.n_states; d.n_classes = dfa.n_classes; d.start = dfa.start;
+    d.table_u16 = dfa.n_states * dfa.n_classes; d.accept_bytes = dfa.n_states;
     auto adv = [&](const char *head) { for (const char *c = head; *c; c++) d.start = dfa.table[(size_t)d.start * dfa.n_classes + dfa.class_of[(uint8_t)*c]]; };
     switch (format) {
         case VG_FMT_P2PKH: case VG_FMT_P2PKH_UNCOMPRESSED: case VG_FMT_P2SH_P2WPKH:
@@ -223,7 +224,7 @@ bool derive_prefixes_from_dfa(const Dfa &d, const char *alpha, std::vector<std::
 }  // namespace
 
 uint32_t dfa_smem_bytes(const vg_dfa_dev &d) {
-    uint64_t tw = ((uint64_t)d.n_states * d.n_classes + 1) / 2, aw = (d.n_states + 3) / 4;
+    uint64_t tw = ((uint64_t)d.table_u16 + 1) / 2, aw = ((uint64_t)d.accept_bytes + 3) / 4;
     uint64_t bytes = (tw + aw + 16) * 4;
     return bytes <= 64 * 1024 ? (uint32_t)bytes : 0;
 }
@@ -268,6 +269,23 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
     if (!compile_pattern(pattern, ci, out.dfa, out.info, err)) { err = "Invalid regex pattern: " + pattern + ": " + err; return false; }   // src/pattern.rs:32-33
     memset(&out.dev, 0, sizeof out.dev);
     fill_device_dfa(format, out.dfa, out.dev.dfa);
+    if (format == VG_FMT_ETHEREUM && (out.dev.dfa.flags & 1u)) {
+        // the pattern tells a-f from A-F, so the device needs the EIP-55 checksum hash of a key before it can run the DFA.
+        // Append the same pattern compiled case-insensitively: it accepts the lower-case hex of every address the pattern
+        // matches, needs no hash, and rejects almost every key (measured: F00$ 1,785 -> see profiles/configs_r01_c.log).
+        Dfa fold; PatternInfo fi; std::string ferr;
+        if (compile_pattern(pattern, true, fold, fi, ferr, true) && out.dfa.table.size() + fold.table.size() < 60000) {
+            vg_dfa_dev fd;
+            fill_device_dfa(format, fold, fd);
+            vg_dfa_dev &d = out.dev.dfa;
+            d.fold_table = (uint32_t)out.dfa.table.size(); d.fold_accept = (uint32_t)out.dfa.accept_end.size();
+            d.fold_classes = fold.n_classes; d.fold_start = fd.start;
+            memcpy(d.fold_sym, fd.sym_class, 16);
+            out.dfa.table.insert(out.dfa.table.end(), fold.table.begin(), fold.table.end());
+            out.dfa.accept_end.insert(out.dfa.accept_end.end(), fold.accept_end.begin(), fold.accept_end.end());
+            d.table_u16 = (uint32_t)out.dfa.table.size(); d.accept_bytes = (uint32_t)out.dfa.accept_end.size();
+        }
+    }
     out.dev.kind = VG_MATCH_DFA;
     out.kind_name = "dfa";
     const PatternInfo &info = out.info;

@@ -23,7 +23,7 @@ struct ParseError { std::string msg; };
 
 class Parser {
 public:
-    Parser(const std::string &s, bool ci) : s_(s), ci_(ci) {}
+    Parser(const std::string &s, bool ci, bool fold_all = false) : s_(s), ci_(ci || fold_all), fold_all_(fold_all) {}
     NodeP parse() {
         NodeP n = alt(0);
         if (pos_ != s_.size()) fail("unopened group");
@@ -32,7 +32,7 @@ public:
 private:
     const std::string &s_;
     size_t pos_ = 0;
-    bool ci_, dotall_ = false;
+    bool ci_, dotall_ = false, fold_all_ = false;
 
     [[noreturn]] void fail(const char *m) { throw ParseError{m}; }
     bool more() const { return pos_ < s_.size(); }
@@ -170,7 +170,7 @@ private:
                         if (f == ':') break;
                         nf++;
                         if (f == '-') negf = true;
-                        else if (f == 'i') ci_ = !negf;
+                        else if (f == 'i') ci_ = fold_all_ || !negf;
                         else if (f == 's') dotall_ = !negf;
                         else if (f == 'm' || f == 'U' || f == 'u' || f == 'R') {}
                         else fail("unsupported flag");
@@ -347,10 +347,10 @@ void analyse(const Node *root, PatternInfo &info) {
 
 }  // namespace
 
-bool compile_pattern(const std::string &pattern, bool ci, Dfa &dfa, PatternInfo &info, std::string &err) {
+bool compile_pattern(const std::string &pattern, bool ci, Dfa &dfa, PatternInfo &info, std::string &err, bool fold_all) {
     if (pattern.empty()) { err = "Pattern cannot be empty"; return false; }   // src/pattern.rs:22-24
     try {
-        Parser p(pattern, ci);
+        Parser p(pattern, ci, fold_all);
         NodeP root = p.parse();
         info = PatternInfo();
         analyse(root.get(), info);

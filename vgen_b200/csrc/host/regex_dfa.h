@@ -32,6 +32,8 @@ struct PatternInfo {
 
 // Returns false and fills err on a syntax error / unsupported construct (same cases as Rust would
 // reject, plus: \b \B, \p{..}, class set operations, flag x, non-ASCII inside classes).
-bool compile_pattern(const std::string &pattern, bool case_insensitive, Dfa &dfa, PatternInfo &info, std::string &err);
+// fold_all: case-insensitive everywhere, inline (?-i) included: the language then contains the lower-cased form of every
+// string the case-sensitive pattern matches (used for the Ethereum prefilter, lowering.cpp)
+bool compile_pattern(const std::string &pattern, bool case_insensitive, Dfa &dfa, PatternInfo &info, std::string &err, bool fold_all = false);
 
 }  // namespace vg

@@ -172,6 +172,16 @@ VG_DEV bool vg_match_eth(const vg_matcher_dev &m, const vg_dfa_view &v, const ui
     uint32_t st = m.dfa.start;
     uint32_t hsh[5] = {0, 0, 0, 0, 0};
     const bool cased = (m.dfa.flags & 1u) != 0;
+    if (cased && m.dfa.fold_table != 0) {
+        // the case-folded pattern on the lower-case hex: a necessary condition that needs no checksum hash
+        uint32_t sf = m.dfa.fold_start;
+        VG_UNROLL for (int i = 0; i < 20; i++) {
+            uint32_t b = (dg[i >> 2] >> (8 * (i & 3))) & 0xffu;
+            sf = v.table[m.dfa.fold_table + sf * m.dfa.fold_classes + m.dfa.fold_sym[b >> 4]];
+            sf = v.table[m.dfa.fold_table + sf * m.dfa.fold_classes + m.dfa.fold_sym[b & 15u]];
+        }
+        if (v.accept[m.dfa.fold_accept + sf] == 0) return false;
+    }
     if (cased) {
         uint32_t msg[10];
         VG_UNROLL for (int w = 0; w < 5; w++) {

@@ -20,6 +20,12 @@ struct vg_dfa_dev {
     uint32_t start;          // start state, already advanced over the fixed head of the address ("bc1q", "0x")
     uint32_t flags;          // bit 0: the DFA tells a-f from A-F (Ethereum: EIP-55 case must be computed on the device)
     uint8_t sym_class[64];   // alphabet index of the format's encoder (base58 digit / bech32 value / hex nibble, +16 = upper case) -> class
+    uint32_t table_u16, accept_bytes;   // sizes of the two arrays as uploaded / staged (the folded DFA below is appended to them)
+    // Ethereum, case-sensitive patterns only: the same pattern compiled case-insensitively, appended behind the exact DFA.
+    // It runs on the lower-case hex first; only keys it accepts pay the EIP-55 checksum Keccak (match.cuh vg_match_eth).
+    uint32_t fold_table, fold_accept;   // offsets of its table (uint16 units) / accept bytes; fold_table == 0: none
+    uint32_t fold_classes, fold_start;
+    uint8_t fold_sym[16];               // nibble -> class of the folded DFA
 };
 struct vg_matcher_dev {
     int kind;

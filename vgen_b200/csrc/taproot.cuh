@@ -19,7 +19,7 @@
 #define VG_TAP_SYNC 1
 #endif
 #ifndef VG_TAP_GROUP
-#define VG_TAP_GROUP 16         // keys handled by one stage-2 thread = keys sharing one field inversion
+#define VG_TAP_GROUP 64         // keys handled by one stage-2 thread = keys sharing one field inversion (<= 64; measured 16: 684, 32: 722, 64: 742 Mkeys/s)
 #endif
 
 // t as 8 big-endian words (t[0] most significant) of the TapTweak tagged hash of the x-only key
@@ -120,7 +120,7 @@ template <int MODE>
 VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsigned long long first) {
     // X_k, Z_k^2 and the running product Z_0^2 ... Z_k^2 (local memory: indexed by the loop counter)
     fe X[VG_TAP_GROUP], Z2[VG_TAP_GROUP], pre[VG_TAP_GROUP];
-    uint32_t ok_mask = 0;
+    unsigned long long ok_mask = 0;
     fe run; fe_set_one(run);
 #ifndef VG_HOST_EMU
     #pragma unroll 1
@@ -152,7 +152,7 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
                 ok = vg_tap_output_key_slow(q, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
             if (ok) { X[k] = q.x; fe_sqr_fast(z2, q.z); }
         }
-        if (ok) ok_mask |= 1u << k;
+        if (ok) ok_mask |= 1ull << k;
         Z2[k] = z2;
         fe_mul(run, run, z2);
         pre[k] = run;
@@ -170,6 +170,6 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
         fe_canon(xq);
         uint32_t dg[VG_DIGEST_WORDS];
         VG_UNROLL for (int i = 0; i < 8; i++) dg[i] = vg_bswap(xq.v[7 - i]);
-        vg_finish_point<VG_FMT_P2TR, MODE>(P, dv, dg, first + (unsigned long long)k, ((ok_mask >> k) & 1u) != 0);
+        vg_finish_point<VG_FMT_P2TR, MODE>(P, dv, dg, first + (unsigned long long)k, ((ok_mask >> k) & 1ull) != 0);
     }
 }
