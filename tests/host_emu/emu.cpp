@@ -2,6 +2,7 @@
 // hash and walk logic can be checked against the oracle on a machine without a GPU.
 // Not part of the product; never used on the GPU path.
 #define VG_HOST_EMU 1
+#define VG_B58_TABLE 1     // the table-driven Base58 conversion is off in the product build; keep it checked here
 #include <vector>
 #include <cstring>
 #include "../../vgen_b200/csrc/taproot.cuh"
@@ -54,6 +55,24 @@ int emu_confirm(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_
     vg_matcher_dev m; memset(&m, 0, sizeof m);
     m.dfa.n_classes = n_classes; m.dfa.start = start; m.dfa.flags = flags;
     vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
+    if (fmt == 2 || fmt == 4) {
+        // segwit formats: the stepwise polymod and the table-driven checksum (what k_walk / k_taptweak use) must agree
+        static uint32_t tab32[32 * 32 + 1], tab52[52 * 32 + 1]; static bool built = false;
+        if (!built) { vg_bech32_fill_table<32>(tab32, 0u, VG_BECH32_CONST, 0, 1); vg_bech32_fill_table<52>(tab52, 1u, VG_BECH32M_CONST, 0, 1); built = true; }
+        int a = fmt == 2 ? vg_confirm<2>(m, dv, dg) : vg_confirm<4>(m, dv, dg);
+        dv.poly = fmt == 2 ? tab32 : tab52;
+        int b = fmt == 2 ? vg_confirm<2>(m, dv, dg) : vg_confirm<4>(m, dv, dg);
+        return a == b ? a : -1;
+    }
+    if (fmt == 0 || fmt == 1 || fmt == 3) {
+        // Base58 formats: long division and the table-driven radix conversion must agree
+        static uint32_t b58[VG_B58_TABLE_WORDS]; static bool built58 = false;
+        if (!built58) { vg_b58_fill_table(b58, 0, 1); built58 = true; }
+        int a = fmt == 3 ? vg_confirm<3>(m, dv, dg) : vg_confirm<0>(m, dv, dg);
+        dv.b58 = b58;
+        int b = fmt == 3 ? vg_confirm<3>(m, dv, dg) : vg_confirm<0>(m, dv, dg);
+        return a == b ? a : -1;
+    }
     switch (fmt) {
         case 0: return vg_confirm<0>(m, dv, dg); case 1: return vg_confirm<1>(m, dv, dg); case 2: return vg_confirm<2>(m, dv, dg);
         case 3: return vg_confirm<3>(m, dv, dg); case 4: return vg_confirm<4>(m, dv, dg); default: return vg_confirm<5>(m, dv, dg);

@@ -192,6 +192,32 @@ def test_device_matcher_vs_host_regex(emu, fmt, pats):
             n_hit += want
 
 
+@pytest.mark.parametrize("fmt", ["p2pkh", "p2sh-p2wpkh", "p2wpkh", "p2tr"])
+def test_encoder_tables_agree_with_stepwise_paths(emu, fmt):
+    """The shared-memory encoder tables of the walk kernels (Base58 radix conversion by column sums, Bech32 checksum by
+    XOR of table rows, match.cuh) against the long-division / stepwise-polymod paths and the oracle's address strings on
+    many digests: emu_confirm runs both device paths and returns -1 when they disagree. The patterns look at the last
+    characters (checksum-dependent) and at a class over the whole string, so every digit reaches the DFA."""
+    import vgen_b200 as vg
+    rng = random.Random(11)
+    F = vg.AddressFormat.parse(fmt)
+    dl = 32 if fmt == "p2tr" else 20
+    digests = [bytes(rng.randrange(256) for _ in range(dl)) for _ in range(3000)]
+    digests += [b"\0" * dl, b"\xff" * dl, b"\0" * (dl - 1) + b"\1", b"\0" * 4 + b"\xff" * (dl - 4), b"\x80" + b"\0" * (dl - 1)]
+    pats = ["[a-m]$", "[2-9]{2}", "^bc1[a-y0-9]+$"] if fmt in ("p2wpkh", "p2tr") else ["[a-m]$", "[1-9]{2}", "^[1-9A-Za-x]+$", "^1{2,}"]
+    emu.emu_confirm.argtypes = [C.c_int, C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint32, C.c_uint32, C.c_uint32]
+    for pat in pats:
+        d = vg.Pattern(pat).device_dfa(F)
+        n_hit = 0
+        for dg in digests:
+            words = (C.c_uint32 * 8)(*[int.from_bytes(dg[4 * i:4 * i + 4].ljust(4, b"\0"), "little") if 4 * i < dl else 0 for i in range(8)])
+            got = emu.emu_confirm(int(F), words, d["table"], d["accept"], d["sym_class"], d["n_classes"], d["start"], d["flags"])
+            want = oracle.regex_match(pat, oracle.address_from_digest(fmt, dg))
+            assert got == int(want), (fmt, pat, dg.hex(), got)
+            n_hit += want
+        assert 0 < n_hit < len(digests) or pat.startswith("^1{2"), (fmt, pat, n_hit)
+
+
 def test_eth_folded_dfa_prefilter(emu):
     """match.cuh vg_match_eth with the case-folded DFA appended (lowering.cpp): the prefilter on the lower-case hex must
     never reject an address the case-sensitive pattern matches, and the combined verdict must equal the host regex."""
