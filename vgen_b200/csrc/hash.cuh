@@ -310,10 +310,54 @@ VG_DEV uint32_t vg_xor3(uint32_t a, uint32_t b, uint32_t c) {
 // VG_KECCAK_UNROLL: 1 = fully unrolled rounds (round-constant loads fold, the zero lanes of the first round and the
 // unused lanes of the last one are eliminated), 0 = rolled loop (smaller code). Measured on B200 (64-bit version):
 // unrolled is 9 % slower (instruction cache).
+// VG_KECCAK_PEEL (rolled loop only): the first and the last round are separate copies of the round body. In the first,
+// 17 of the 25 input lanes are zero or padding constants and fold away; in the last, only row 0 of the state is read by
+// the callers (lanes 0..3), so 20 of the 25 rho/pi lanes and 4 of the 5 chi rows are dead code. After keccak_f1600 only
+// lanes 0..4 are meaningful.
 #ifndef VG_KECCAK_UNROLL
 #define VG_KECCAK_UNROLL 0
 #endif
+#ifndef VG_KECCAK_PEEL
+#define VG_KECCAK_PEEL 1
+#endif
+VG_DEV void keccak_round(uint32_t sl[25], uint32_t sh[25], uint32_t rc_l, uint32_t rc_h) {
+    uint32_t cl[5], ch[5];
+    VG_UNROLL for (int x = 0; x < 5; x++) {
+        cl[x] = vg_xor3(vg_xor3(sl[x], sl[x + 5], sl[x + 10]), sl[x + 15], sl[x + 20]);
+        ch[x] = vg_xor3(vg_xor3(sh[x], sh[x + 5], sh[x + 10]), sh[x + 15], sh[x + 20]);
+    }
+    // for column x: ca = c[x-1], r1 = rotl64(c[x+1], 1)
+    uint32_t ca_l[5], ca_h[5], r1_l[5], r1_h[5];
+    VG_UNROLL for (int x = 0; x < 5; x++) {
+        ca_l[x] = cl[(x + 4) % 5]; ca_h[x] = ch[(x + 4) % 5];
+        vg_rotl64_halves<1>(r1_l[x], r1_h[x], cl[(x + 1) % 5], ch[(x + 1) % 5]);
+    }
+    uint32_t bl[25], bh[25];
+    VG_K_RHO(0, 0, 0);
+    VG_K_RHO(10, 1, 1);   VG_K_RHO(20, 2, 62);  VG_K_RHO(5, 3, 28);   VG_K_RHO(15, 4, 27);
+    VG_K_RHO(16, 5, 36);  VG_K_RHO(1, 6, 44);   VG_K_RHO(11, 7, 6);   VG_K_RHO(21, 8, 55);
+    VG_K_RHO(6, 9, 20);   VG_K_RHO(7, 10, 3);   VG_K_RHO(17, 11, 10); VG_K_RHO(2, 12, 43);
+    VG_K_RHO(12, 13, 25); VG_K_RHO(22, 14, 39); VG_K_RHO(23, 15, 41); VG_K_RHO(8, 16, 45);
+    VG_K_RHO(18, 17, 15); VG_K_RHO(3, 18, 21);  VG_K_RHO(13, 19, 8);  VG_K_RHO(14, 20, 18);
+    VG_K_RHO(24, 21, 2);  VG_K_RHO(9, 22, 61);  VG_K_RHO(19, 23, 56); VG_K_RHO(4, 24, 14);
+    VG_UNROLL for (int j = 0; j < 25; j += 5) {
+        VG_UNROLL for (int x = 0; x < 5; x++) {
+            sl[j + x] = bl[j + x] ^ (~bl[j + (x + 1) % 5] & bl[j + (x + 2) % 5]);
+            sh[j + x] = bh[j + x] ^ (~bh[j + (x + 1) % 5] & bh[j + (x + 2) % 5]);
+        }
+    }
+    sl[0] ^= rc_l;
+    sh[0] ^= rc_h;
+}
 VG_DEV void keccak_f1600(uint32_t sl[25], uint32_t sh[25]) {
+#if VG_KECCAK_PEEL && !VG_KECCAK_UNROLL
+    keccak_round(sl, sh, 0x00000001u, 0u);                                  // round 0
+  #ifndef VG_HOST_EMU
+    #pragma unroll 1
+  #endif
+    for (int r = 1; r < 23; r++) keccak_round(sl, sh, (uint32_t)VG_KECCAK_RC[r], (uint32_t)(VG_KECCAK_RC[r] >> 32));
+    keccak_round(sl, sh, 0x80008008u, 0x80000000u);                         // round 23
+#else
 #if VG_KECCAK_UNROLL && !defined(VG_HOST_EMU)
     #pragma unroll
 #else
@@ -321,35 +365,8 @@ VG_DEV void keccak_f1600(uint32_t sl[25], uint32_t sh[25]) {
     #pragma unroll 1
   #endif
 #endif
-    for (int r = 0; r < 24; r++) {
-        uint32_t cl[5], ch[5];
-        VG_UNROLL for (int x = 0; x < 5; x++) {
-            cl[x] = vg_xor3(vg_xor3(sl[x], sl[x + 5], sl[x + 10]), sl[x + 15], sl[x + 20]);
-            ch[x] = vg_xor3(vg_xor3(sh[x], sh[x + 5], sh[x + 10]), sh[x + 15], sh[x + 20]);
-        }
-        // for column x: ca = c[x-1], r1 = rotl64(c[x+1], 1)
-        uint32_t ca_l[5], ca_h[5], r1_l[5], r1_h[5];
-        VG_UNROLL for (int x = 0; x < 5; x++) {
-            ca_l[x] = cl[(x + 4) % 5]; ca_h[x] = ch[(x + 4) % 5];
-            vg_rotl64_halves<1>(r1_l[x], r1_h[x], cl[(x + 1) % 5], ch[(x + 1) % 5]);
-        }
-        uint32_t bl[25], bh[25];
-        VG_K_RHO(0, 0, 0);
-        VG_K_RHO(10, 1, 1);   VG_K_RHO(20, 2, 62);  VG_K_RHO(5, 3, 28);   VG_K_RHO(15, 4, 27);
-        VG_K_RHO(16, 5, 36);  VG_K_RHO(1, 6, 44);   VG_K_RHO(11, 7, 6);   VG_K_RHO(21, 8, 55);
-        VG_K_RHO(6, 9, 20);   VG_K_RHO(7, 10, 3);   VG_K_RHO(17, 11, 10); VG_K_RHO(2, 12, 43);
-        VG_K_RHO(12, 13, 25); VG_K_RHO(22, 14, 39); VG_K_RHO(23, 15, 41); VG_K_RHO(8, 16, 45);
-        VG_K_RHO(18, 17, 15); VG_K_RHO(3, 18, 21);  VG_K_RHO(13, 19, 8);  VG_K_RHO(14, 20, 18);
-        VG_K_RHO(24, 21, 2);  VG_K_RHO(9, 22, 61);  VG_K_RHO(19, 23, 56); VG_K_RHO(4, 24, 14);
-        VG_UNROLL for (int j = 0; j < 25; j += 5) {
-            VG_UNROLL for (int x = 0; x < 5; x++) {
-                sl[j + x] = bl[j + x] ^ (~bl[j + (x + 1) % 5] & bl[j + (x + 2) % 5]);
-                sh[j + x] = bh[j + x] ^ (~bh[j + (x + 1) % 5] & bh[j + (x + 2) % 5]);
-            }
-        }
-        sl[0] ^= (uint32_t)VG_KECCAK_RC[r];
-        sh[0] ^= (uint32_t)(VG_KECCAK_RC[r] >> 32);
-    }
+    for (int r = 0; r < 24; r++) keccak_round(sl, sh, (uint32_t)VG_KECCAK_RC[r], (uint32_t)(VG_KECCAK_RC[r] >> 32));
+#endif
 }
 // Ethereum address words: Keccak-256(X || Y)[12..32] as 5 words, digest byte 4i+j = byte j of out[i]
 VG_DEV void keccak_eth_address(uint32_t out[5], const fe &x, const fe &y) {
