@@ -42,7 +42,8 @@ VG_DEV bool vg_tweak_is_valid(const uint32_t t[8]) {
 }
 // r = a + (bx, by) for a finite Jacobian a, generic case only (8M + 3S, no calls). Returns false when the two points share
 // their x coordinate (doubling / opposite points): the caller then redoes the key with the complete formulas.
-VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
+// need_y = false (the last table window: only X and Z of the sum are used) skips the two multiplications of Y3.
+VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by, bool need_y = true) {
     fe z2, u2, s2, h, rr, h2, h3, v, t;
     fe_sqr_fast(z2, a.z); fe_mul(u2, bx, z2);
     fe_mul(s2, by, z2); fe_mul(s2, s2, a.z);
@@ -51,9 +52,29 @@ VG_DEV bool vg_gej_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
     if (fe_is_zero_raw(hc)) return false;
     fe_sqr_fast(h2, h); fe_mul(h3, h2, h); fe_mul(v, a.x, h2);
     fe_sqr_fast(t, rr); fe_sub(t, t, h3); fe_sub(t, t, v); fe_sub(t, t, v);      // X3
-    fe_sub(v, v, t); fe_mul(v, rr, v); fe_mul(h3, a.y, h3); fe_sub(a.y, v, h3);
+    if (need_y) { fe_sub(v, v, t); fe_mul(v, rr, v); fe_mul(h3, a.y, h3); fe_sub(a.y, v, h3); }
     a.x = t;
     fe_mul(a.z, a.z, h);
+    return true;
+}
+// The same for a.z == 1 (the first table addition of a key: P is affine): 4M + 2S. VG_TAP_FIRST_AFFINE = 0 switches it off.
+#ifndef VG_TAP_FIRST_AFFINE
+#define VG_TAP_FIRST_AFFINE 1
+#endif
+// VG_TAP_LAST_NO_Y: the addition of the top table window leaves Y3 out (the caller reads only X and Z of Q)
+#ifndef VG_TAP_LAST_NO_Y
+#define VG_TAP_LAST_NO_Y 1
+#endif
+VG_DEV bool vg_aff_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
+    fe h, rr, h2, h3, v, t;
+    fe_sub(h, bx, a.x); fe_sub(rr, by, a.y);
+    fe hc = h; fe_canon(hc);
+    if (fe_is_zero_raw(hc)) return false;
+    fe_sqr_fast(h2, h); fe_mul(h3, h2, h); fe_mul(v, a.x, h2);
+    fe_sqr_fast(t, rr); fe_sub(t, t, h3); fe_sub(t, t, v); fe_sub(t, t, v);      // X3
+    fe_sub(v, v, t); fe_mul(v, rr, v); fe_mul(h3, a.y, h3); fe_sub(a.y, v, h3);
+    a.x = t;
+    a.z = h;
     return true;
 }
 
@@ -79,12 +100,13 @@ VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t j, uint32_t bits) {
 }
 
 // Q = P + t*G in Jacobian coordinates. Returns false when Q is the point at infinity (t*G = -P).
-// FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false).
+// FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false);
+// q.y is then not computed for the top window (VG_TAP_LAST_NO_Y): only q.x and q.z are meaningful.
 // FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
 template <bool FAST>
 VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true) {
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
-    bool special = false;
+    bool special = false, affine = true;        // affine: q.z is still 1
     const uint32_t n_win = vg_tap_windows(bits), mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
 #ifndef VG_HOST_EMU
     #pragma unroll 1
@@ -105,7 +127,10 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
         bx.v[0] = a0.x; bx.v[1] = a0.y; bx.v[2] = a0.z; bx.v[3] = a0.w; bx.v[4] = a1.x; bx.v[5] = a1.y; bx.v[6] = a1.z; bx.v[7] = a1.w;
         by.v[0] = a2.x; by.v[1] = a2.y; by.v[2] = a2.z; by.v[3] = a2.w; by.v[4] = a3.x; by.v[5] = a3.y; by.v[6] = a3.z; by.v[7] = a3.w;
 #endif
-        if (FAST) { if (!vg_gej_add_affine_fast(q, bx, by)) special = true; }
+        if (FAST) {
+            if (VG_TAP_FIRST_AFFINE && affine) { if (!vg_aff_add_affine_fast(q, bx, by)) special = true; affine = false; }
+            else if (!vg_gej_add_affine_fast(q, bx, by, !VG_TAP_LAST_NO_Y || j + 1 < n_win)) special = true;
+        }
         else { gej_t r; gej_add_affine(r, q, bx, by); q = r; if (q.inf) { fe_set_one(q.z); } }
     }
     return !q.inf && !special;
