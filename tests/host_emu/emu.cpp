@@ -78,6 +78,17 @@ int emu_confirm(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_
         case 3: return vg_confirm<3>(m, dv, dg); case 4: return vg_confirm<4>(m, dv, dg); default: return vg_confirm<5>(m, dv, dg);
     }
 }
+// segwit matcher with the checksum-suffix prefilter (vg_dfa_dev::chk_mask / chk_value) on the table path
+int emu_confirm_chk(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_t *accept, const uint8_t *sym_class,
+                    uint32_t n_classes, uint32_t start, uint32_t flags, uint32_t chk_mask, uint32_t chk_value) {
+    vg_matcher_dev m; memset(&m, 0, sizeof m);
+    m.dfa.n_classes = n_classes; m.dfa.start = start; m.dfa.flags = flags; m.dfa.chk_mask = chk_mask; m.dfa.chk_value = chk_value;
+    vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
+    static uint32_t tab32[32 * 32 + 1], tab52[52 * 32 + 1]; static bool built = false;
+    if (!built) { vg_bech32_fill_table<32>(tab32, 0u, VG_BECH32_CONST, 0, 1); vg_bech32_fill_table<52>(tab52, 1u, VG_BECH32M_CONST, 0, 1); built = true; }
+    dv.poly = fmt == 2 ? tab32 : tab52;
+    return fmt == 2 ? vg_confirm<2>(m, dv, dg) : vg_confirm<4>(m, dv, dg);
+}
 // Ethereum matcher with the case-folded DFA appended behind the exact one (lowering.cpp): table / accept hold both
 int emu_confirm_eth_fold(const uint32_t *dg, const uint16_t *table, const uint8_t *accept, const uint8_t *sym_class,
                          uint32_t n_classes, uint32_t start, uint32_t flags, uint32_t fold_table, uint32_t fold_accept,

@@ -218,6 +218,36 @@ def test_encoder_tables_agree_with_stepwise_paths(emu, fmt):
         assert 0 < n_hit < len(digests) or pat.startswith("^1{2"), (fmt, pat, n_hit)
 
 
+@pytest.mark.parametrize("fmt", ["p2wpkh", "p2tr"])
+def test_segwit_checksum_suffix_prefilter(emu, fmt):
+    """Literal-suffix patterns on segwit formats (dead$): the device tests the checksum bits first and runs the DFA only on
+    keys that pass (vg_dfa_dev::chk_mask / chk_value, lowering.cpp). Short suffixes so that random digests hit; the verdict
+    must equal the oracle's regex over the address string, for matching and non-matching keys alike."""
+    import vgen_b200 as vg
+    CH = "qpzry9x8gf2tvdw0s3jn54khce6mua7l"
+    rng = random.Random(23)
+    F = vg.AddressFormat.parse(fmt)
+    dl = 32 if fmt == "p2tr" else 20
+    digests = [bytes(rng.randrange(256) for _ in range(dl)) for _ in range(3000)] + [b"\0" * dl, b"\xff" * dl]
+    emu.emu_confirm_chk.argtypes = [C.c_int, C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p] + [C.c_uint32] * 5
+    # one pattern is the real suffix of a digest's address, so a 6-character case matches at least once
+    full = oracle.address_from_digest(fmt, digests[7])[-6:]
+    for pat in ["q$", "e$", full[-2:] + "$", full[-3:] + "$", full + "$"]:
+        lit = pat[:-1]
+        mask, value = (1 << (5 * len(lit))) - 1, 0
+        for ch in lit:
+            value = (value << 5) | CH.index(ch)
+        d = vg.Pattern(pat).device_dfa(F)
+        n_hit = 0
+        for dg in digests:
+            words = (C.c_uint32 * 8)(*[int.from_bytes(dg[4 * i:4 * i + 4].ljust(4, b"\0"), "little") if 4 * i < dl else 0 for i in range(8)])
+            got = emu.emu_confirm_chk(int(F), words, d["table"], d["accept"], d["sym_class"], d["n_classes"], d["start"], d["flags"], mask, value)
+            want = oracle.regex_match(pat, oracle.address_from_digest(fmt, dg))
+            assert got == int(want), (fmt, pat, dg.hex())
+            n_hit += want
+        assert n_hit > 0, (fmt, pat)
+
+
 def test_eth_folded_dfa_prefilter(emu):
     """match.cuh vg_match_eth with the case-folded DFA appended (lowering.cpp): the prefilter on the lower-case hex must
     never reject an address the case-sensitive pattern matches, and the combined verdict must equal the host regex."""

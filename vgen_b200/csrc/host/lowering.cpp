@@ -286,6 +286,21 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             d.table_u16 = (uint32_t)out.dfa.table.size(); d.accept_bytes = (uint32_t)out.dfa.accept_end.size();
         }
     }
+    if (format == VG_FMT_P2WPKH || format == VG_FMT_P2TR) {
+        // "dead$": a literal of 1..6 Bech32 characters anchored at the end lies inside the checksum symbols
+        static const char *charset = "qpzry9x8gf2tvdw0s3jn54khce6mua7l";
+        const size_t n = pattern.size();
+        if (n >= 2 && n <= 7 && pattern[n - 1] == '$') {
+            uint32_t value = 0; bool ok = true;
+            for (size_t i = 0; i + 1 < n && ok; i++) {
+                char c = pattern[i];
+                if (ci && c >= 'A' && c <= 'Z') c = (char)(c - 'A' + 'a');
+                const char *q = strchr(charset, c);
+                if (c == 0 || !q) ok = false; else value = (value << 5) | (uint32_t)(q - charset);
+            }
+            if (ok) { out.dev.dfa.chk_mask = (1u << (5 * (n - 1))) - 1u; out.dev.dfa.chk_value = value; }
+        }
+    }
     out.dev.kind = VG_MATCH_DFA;
     out.kind_name = "dfa";
     const PatternInfo &info = out.info;

@@ -230,7 +230,26 @@ VG_DEV bool vg_match_segwit(const vg_matcher_dev &m, const vg_dfa_view &v, const
     const uint32_t nc = m.dfa.n_classes;
     uint32_t st = m.dfa.start;
     uint32_t chk;
-    if (v.poly) {
+    if (v.poly && m.dfa.chk_mask) {
+        // literal-suffix patterns: the checksum alone decides all but one key in 32^k; only those run the DFA
+        chk = v.poly[NSYM * 32];
+        VG_UNROLL for (int j = 0; j < NSYM; j++) {
+            const int bit = 5 * j, wi = bit >> 5, off = bit & 31;
+            uint32_t val = off <= 27 ? (B[wi] >> (27 - off)) & 31u : ((B[wi] << (off - 27)) | (B[wi + 1] >> (59 - off))) & 31u;
+            chk ^= v.poly[32 * j + val];
+        }
+        if ((chk & m.dfa.chk_mask) != m.dfa.chk_value) return false;
+#ifndef VG_HOST_EMU
+        #pragma unroll 1
+#endif
+        for (int j = 0; j < NSYM; j++) {
+            const uint32_t bit = 5u * (uint32_t)j, wi = bit >> 5, off = bit & 31u;
+            uint32_t w0 = 0, w1 = 0;
+            VG_UNROLL for (int i = 0; i < ((NSYM - 1) * 5) / 32 + 1; i++) { w0 = (wi == (uint32_t)i) ? B[i] : w0; w1 = (wi == (uint32_t)i) ? B[i + 1] : w1; }
+            unsigned long long two = ((unsigned long long)w0 << 32) | w1;
+            st = vg_dfa_step(v, nc, st, v.sym[(uint32_t)(two >> (59u - off)) & 31u]);
+        }
+    } else if (v.poly) {
         chk = v.poly[NSYM * 32];
         VG_UNROLL for (int j = 0; j < NSYM; j++) {
             const int bit = 5 * j, wi = bit >> 5, off = bit & 31;

@@ -26,6 +26,10 @@ struct vg_dfa_dev {
     uint32_t fold_table, fold_accept;   // offsets of its table (uint16 units) / accept bytes; fold_table == 0: none
     uint32_t fold_classes, fold_start;
     uint8_t fold_sym[16];               // nibble -> class of the folded DFA
+    // Segwit formats, patterns that are a literal suffix of at most 6 characters (dead$): the match lies inside the 6 checksum
+    // symbols, so (checksum & chk_mask) == chk_value is a necessary condition that needs no DFA step (match.cuh
+    // vg_match_segwit); chk_mask == 0: none.
+    uint32_t chk_mask, chk_value;
 };
 struct vg_matcher_dev {
     int kind;
