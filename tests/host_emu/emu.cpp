@@ -86,6 +86,7 @@ int emu_confirm_chk(int fmt, const uint32_t *dg, const uint16_t *table, const ui
     vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
     static uint32_t tab32[32 * 32 + 1], tab52[52 * 32 + 1]; static bool built = false;
     if (!built) { vg_bech32_fill_table<32>(tab32, 0u, VG_BECH32_CONST, 0, 1); vg_bech32_fill_table<52>(tab52, 1u, VG_BECH32M_CONST, 0, 1); built = true; }
+    if (fmt == 5) return vg_confirm<5>(m, dv, dg);       // Ethereum: mask over the last 32 digest bits
     dv.poly = fmt == 2 ? tab32 : tab52;
     return fmt == 2 ? vg_confirm<2>(m, dv, dg) : vg_confirm<4>(m, dv, dg);
 }

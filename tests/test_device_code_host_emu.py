@@ -248,6 +248,29 @@ def test_segwit_checksum_suffix_prefilter(emu, fmt):
         assert n_hit > 0, (fmt, pat)
 
 
+def test_eth_literal_suffix_prefilter(emu):
+    """Ethereum literal hex suffixes (F00$, 12$): the device compares the last digest bits with the lower-cased literal before
+    the DFAs and the EIP-55 hash. The verdict must equal the oracle's regex over the checksummed address."""
+    import vgen_b200 as vg
+    rng = random.Random(29)
+    F = vg.AddressFormat.parse("ethereum")
+    digests = [bytes(rng.randrange(256) for _ in range(20)) for _ in range(3000)]
+    digests += [d[:18] + bytes.fromhex("af00") for d in digests[:200]] + [d[:16] + bytes.fromhex("deadbeef") for d in digests[:50]]
+    emu.emu_confirm_chk.argtypes = [C.c_int, C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p] + [C.c_uint32] * 5
+    for pat, ci in [("F00$", False), ("f00$", False), ("12$", False), ("a$", False), ("dEaDbEeF$", True), ("DEADBEEF$", False), ("00$", False)]:
+        lit = pat[:-1]
+        mask = (1 << (4 * len(lit))) - 1
+        d = vg.Pattern(pat, ci).device_dfa(F)
+        n_hit = 0
+        for dg in digests:
+            words = (C.c_uint32 * 8)(*[int.from_bytes(dg[4 * i:4 * i + 4], "little") if i < 5 else 0 for i in range(8)])
+            got = emu.emu_confirm_chk(int(F), words, d["table"], d["accept"], d["sym_class"], d["n_classes"], d["start"], d["flags"], mask, int(lit, 16))
+            want = oracle.regex_match(("(?i)" if ci else "") + pat, oracle.address_from_digest("ethereum", dg))
+            assert got == int(want), (pat, dg.hex())
+            n_hit += want
+        assert n_hit > 0 or pat == "DEADBEEF$", (pat, n_hit)
+
+
 def test_eth_folded_dfa_prefilter(emu):
     """match.cuh vg_match_eth with the case-folded DFA appended (lowering.cpp): the prefilter on the lower-case hex must
     never reject an address the case-sensitive pattern matches, and the combined verdict must equal the host regex."""

@@ -123,6 +123,9 @@ def _check_scan(runner, fmt, pat, start, n, ci=False):
     ("ethereum", "^0x(de|be)a", False), ("p2tr", "^bc1p(qq|pp)", False), ("p2sh-p2wpkh", "^(3Ab|3Cd)$", False),
     # Ethereum case-sensitive patterns: the case-folded DFA runs first, the EIP-55 hash only for keys it accepts
     ("ethereum", "[A-F]{3}$", False), ("ethereum", "(?-i:aB)", False), ("ethereum", "e$", False), ("ethereum", "Ab|cD", False),
+    # literal suffixes: tested on the Bech32 checksum bits / the last digest bits before any DFA step (vg_dfa_dev::chk_mask)
+    ("p2wpkh", "qq$", False), ("p2wpkh", "ZQ$", True), ("p2tr", "7$", False), ("ethereum", "1f$", False), ("ethereum", "AB$", True),
+    ("ethereum", "AB$", False), ("ethereum", "07$", False),
 ])
 def test_scan_match_sets_small(small_runner, fmt, pat, ci):
     _check_scan(small_runner, fmt, pat, 2**64, 1 << 18, ci)

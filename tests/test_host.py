@@ -254,3 +254,30 @@ def test_match_list_is_a_lazy_sequence():
     assert len(m) == 2 and m._items is None                    # len() does not parse
     assert m[0] == vg.GeneratedAddress("1Abc", "Kx1", "00aa", vg.AddressFormat.P2pkh) and m[-1].hex == "00bb"
     assert [x.address for x in m] == ["1Abc", "1Def"] and m == list(m) and len(MatchList(b"", 0, vg.AddressFormat.P2pkh)) == 0
+
+
+def test_literal_suffix_lowering():
+    """dead$ on segwit formats / F00$ on Ethereum: the DFA stays the decider, and the host adds a (mask, value) test over the
+    six Bech32 checksum symbols / the last 32 digest bits that the device runs first (lowering.cpp, scan_types.h)."""
+    F = vg.AddressFormat
+    CH = "qpzry9x8gf2tvdw0s3jn54khce6mua7l"
+    def bech(lit):
+        v = 0
+        for ch in lit:
+            v = (v << 5) | CH.index(ch)
+        return ((1 << (5 * len(lit))) - 1, v)
+    for fmt in (F.P2wpkh, F.P2tr):
+        for lit in ("dead", "q", "zzzzzz", "7l"):
+            low = vg.Pattern(lit + "$").lowering(fmt)
+            assert low["kind"] == "dfa" and low["suffix"] == bech(lit), (fmt, lit, low)
+        assert vg.Pattern("DEAD$", True).lowering(fmt)["suffix"] == bech("dead")
+        # not literal suffixes of Bech32 characters (b, i, o, 1 are not in the alphabet), too long, upper case without -i
+        for pat in ("de.d$", "dead", "^dead$", "bead$", "qqqqqqq$", "DEAD$", "d[e]ad$", "$"):
+            assert vg.Pattern(pat).lowering(fmt)["suffix"] is None, (fmt, pat)
+    for lit in ("F00", "f00", "dEaD", "12345678", "0"):
+        low = vg.Pattern(lit + "$").lowering(F.Ethereum)
+        assert low["kind"] == "dfa" and low["suffix"] == ((1 << (4 * len(lit))) - 1, int(lit, 16)), (lit, low)
+    for pat in ("g00$", "123456789$", "f.0$", "^0xf00$", "f00"):
+        assert vg.Pattern(pat).lowering(F.Ethereum)["suffix"] is None, pat
+    for fmt in (F.P2pkh, F.P2shP2wpkh, F.P2pkhUncompressed):
+        assert vg.Pattern("dead$").lowering(fmt)["suffix"] is None

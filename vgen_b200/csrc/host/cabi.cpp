@@ -269,6 +269,10 @@ int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, si
         s += ";exact=";
         for (int i = 0; i < lp.dev.exact_words * 4; i++) { snprintf(buf, sizeof buf, "%02x", (lp.dev.exact[i / 4] >> (8 * (i % 4))) & 0xff); s += buf; }
     }
+    if (lp.dev.kind == VG_MATCH_DFA && lp.dev.dfa.chk_mask != 0) {      // literal-suffix test ahead of the DFA (scan_types.h)
+        snprintf(buf, sizeof buf, ";suffix=%08x:%08x", lp.dev.dfa.chk_mask, lp.dev.dfa.chk_value);
+        s += buf;
+    }
     return copy_out(s, out, cap);
 }
 

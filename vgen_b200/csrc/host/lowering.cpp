@@ -301,6 +301,21 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             if (ok) { out.dev.dfa.chk_mask = (1u << (5 * (n - 1))) - 1u; out.dev.dfa.chk_value = value; }
         }
     }
+    if (format == VG_FMT_ETHEREUM) {
+        // "F00$", "dead$": a literal of 1..8 hex digits anchored at the end. Whatever the EIP-55 case turns out to be, the
+        // lower-case hex of a matching address ends with the lower-cased literal: a test on the last digest bits.
+        const size_t n = pattern.size();
+        if (n >= 2 && n <= 9 && pattern[n - 1] == '$') {
+            uint32_t value = 0; bool ok = true;
+            for (size_t i = 0; i + 1 < n && ok; i++) {
+                const char c = pattern[i];
+                uint32_t d = (c >= '0' && c <= '9') ? (uint32_t)(c - '0') : (c >= 'a' && c <= 'f') ? (uint32_t)(c - 'a' + 10)
+                           : (c >= 'A' && c <= 'F') ? (uint32_t)(c - 'A' + 10) : 16u;
+                if (d > 15u) ok = false; else value = (value << 4) | d;
+            }
+            if (ok) { out.dev.dfa.chk_mask = n - 1 == 8 ? 0xffffffffu : (1u << (4 * (n - 1))) - 1u; out.dev.dfa.chk_value = value; }
+        }
+    }
     out.dev.kind = VG_MATCH_DFA;
     out.kind_name = "dfa";
     const PatternInfo &info = out.info;

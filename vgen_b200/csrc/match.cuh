@@ -295,6 +295,8 @@ VG_DEV bool vg_match_eth(const vg_matcher_dev &m, const vg_dfa_view &v, const ui
     uint32_t st = m.dfa.start;
     uint32_t hsh[5] = {0, 0, 0, 0, 0};
     const bool cased = (m.dfa.flags & 1u) != 0;
+    // literal hex suffix: the last digest bits decide all but one key in 16^k
+    if (m.dfa.chk_mask != 0 && (vg_bswap(dg[4]) & m.dfa.chk_mask) != m.dfa.chk_value) return false;
     if (cased && m.dfa.fold_table != 0) {
         // the case-folded pattern on the lower-case hex: a necessary condition that needs no checksum hash
         uint32_t sf = m.dfa.fold_start;

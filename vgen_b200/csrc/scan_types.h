@@ -28,7 +28,8 @@ struct vg_dfa_dev {
     uint8_t fold_sym[16];               // nibble -> class of the folded DFA
     // Segwit formats, patterns that are a literal suffix of at most 6 characters (dead$): the match lies inside the 6 checksum
     // symbols, so (checksum & chk_mask) == chk_value is a necessary condition that needs no DFA step (match.cuh
-    // vg_match_segwit); chk_mask == 0: none.
+    // vg_match_segwit); chk_mask == 0: none. Ethereum, literal hex suffixes of at most 8 digits (F00$): the same pair over the last
+    // 32 digest bits (big-endian), tested before the DFAs and the EIP-55 hash (vg_match_eth).
     uint32_t chk_mask, chk_value;
 };
 struct vg_matcher_dev {

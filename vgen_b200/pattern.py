@@ -40,16 +40,18 @@ class Pattern:
         return int(_cabi.lib().vgen_pattern_estimate_difficulty(int(fmt), self._pattern.encode(), int(self._ci)))
 
     def lowering(self, fmt):
-        """How the scan path will test this pattern on the device for `fmt`: dict(kind=..., intervals=[(lo, hi), ...])."""
+        """How the scan path will test this pattern on the device for `fmt`: dict(kind=..., intervals=[(lo, hi), ...], exact=..., suffix=(mask, value) or None)."""
         buf = C.create_string_buffer(4096)
         rc = _cabi.lib().vgen_pattern_lowering(int(fmt), self._pattern.encode(), int(self._ci), buf, 4096)
         if rc < 0:
             raise _cabi.VgenError(rc, "vgen_pattern_lowering")
         parts = buf.value.decode().split(";")
-        out = {"kind": parts[0], "intervals": [], "exact": None}
+        out = {"kind": parts[0], "intervals": [], "exact": None, "suffix": None}
         for p in parts[1:]:
             if p.startswith("exact="):
                 out["exact"] = bytes.fromhex(p[6:])
+            elif p.startswith("suffix="):       # (mask, value) over the Bech32 checksum bits / the last 32 digest bits
+                out["suffix"] = tuple(int(x, 16) for x in p[7:].split(":"))
             elif p:
                 lo, hi = p.split("-")
                 out["intervals"].append((int(lo, 16), int(hi, 16)))
