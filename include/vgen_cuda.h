@@ -114,6 +114,11 @@ int vgen_cuda_lane_count(const vgen_ctx *ctx);
 /* window width (bits) of the P2TR fixed-base table this context has built: 0 none yet, 16 for short jobs, 24 for jobs of
  * at least 2^30 keys, 26 from 2^36 keys (or what VGEN_TAP_BITS forces); a wider table is kept once built */
 int vgen_cuda_tap_bits(const vgen_ctx *ctx);
+/* Counters of the context, for tests and run reports: out[0] devices, out[1] devices that have dropped out after a CUDA error
+ * (their windows were taken over by the others; VGEN_FAULT_INJECT=<device index>:<n> makes the n-th window issue of a device
+ * fail that way), out[2] windows taken over from a failed device, out[3] windows whose hits exceeded the per-slot hit buffer and
+ * were re-run in pieces, out[4] hit records per slot buffer, out[5] confirm worker threads, out[6..7] reserved (0). */
+void vgen_cuda_stats(const vgen_ctx *ctx, uint64_t out[8]);
 /* bytes the scans of this context copied host->device (start scalars, launch parameters) and device->host (counters, hit records) */
 void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h);
 

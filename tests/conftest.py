@@ -10,6 +10,7 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu on the GPU box")
+    config.addinivalue_line("markers", "slow: full-size BASELINE configs (minutes on one B200); deselect with -m 'gpu and not slow'")
 
 
 @pytest.fixture(scope="session")

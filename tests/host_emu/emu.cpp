@@ -11,7 +11,7 @@ static const uint32_t G_XY[16] = {
     0x16F81798, 0x59F2815B, 0x2DCE28D9, 0x029BFCDB, 0xCE870B07, 0x55A06295, 0xF9DCBBAC, 0x79BE667E,
     0xFB10D4B8, 0x9C47D08F, 0xA6855419, 0xFD17B448, 0x0E1108A8, 0x5DA4FBFC, 0x26A3C465, 0x483ADA77};
 static std::vector<uint32_t> g_pow2;
-static void ensure_pow2() { if (g_pow2.empty()) { g_pow2.resize(256 * 16); vg_build_pow2(g_pow2.data(), G_XY); } }
+static void ensure_pow2() { if (g_pow2.empty()) { g_pow2.resize(256 * 16); std::vector<uint32_t> scratch(256 * 32); vg_build_pow2(g_pow2.data(), G_XY, scratch.data()); } }
 
 extern "C" {
 void emu_fe_mul(const uint32_t *a, const uint32_t *b, uint32_t *r) { fe x, y, z; memcpy(x.v, a, 32); memcpy(y.v, b, 32); fe_mul(z, x, y); fe_canon(z); memcpy(r, z.v, 32); }

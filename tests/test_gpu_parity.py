@@ -95,7 +95,7 @@ def test_multi_window_walk_consistency(small_runner):
     assert hashlib.sha256(got).hexdigest() == hashlib.sha256(b"".join(small_runner.generate_batch(start, n))).hexdigest()
 
 
-def _scan(runner, fmt, pat, start, n, ci=False, count=0):
+def _scan(runner, fmt, pat, start, n, ci=False, count=vg.UNLIMITED):
     cfg = vg.ScanConfig(format=vg.AddressFormat.parse(fmt), count=count, start=start, end=start + n - 1)
     return vg.scan_gpu_with_runner(vg.Pattern(pat, ci), cfg, None, None, runner)
 
@@ -111,24 +111,43 @@ def _check_scan(runner, fmt, pat, start, n, ci=False):
     return res
 
 
-@pytest.mark.parametrize("fmt,pat,ci", [
+# (format, pattern, case-insensitive, keys): every case has a NON-EMPTY oracle set on [2^64, 2^64 + keys) (asserted), so no
+# case compares [] with []; patterns that can never match are in test_scan_patterns_that_cannot_match below.
+SMALL_CASES = [
     ("p2pkh", "^1Ca", False), ("p2pkh", "^1cat", True), ("p2pkh", "^1[Cc]a", False), ("p2pkh", "^11", False),
     ("p2pkh-uncompressed", "^1Ab", False), ("p2sh-p2wpkh", "^3Ab", False), ("p2sh-p2wpkh", "^3", False),
-    ("p2wpkh", "^bc1qaa", False), ("p2wpkh", "dead$", False), ("p2wpkh", "aa.*zz", False),
+    ("p2wpkh", "^bc1qaa", False), ("p2wpkh", "ead$", False), ("p2wpkh", "aa.*zz", False),
     ("ethereum", "^0xdea", False), ("ethereum", "^0xDe", False), ("ethereum", "^0xab", True), ("ethereum", "F00$", False),
-    ("p2tr", "^bc1pqq", False), ("p2tr", "dead$", False), ("p2tr", "^bc1p.*zzz", False), ("p2tr", "^bc1q", False),
-    ("p2pkh", "abc$", False), ("p2pkh", "[0-9]{4}$", False), ("p2pkh", "^1.*XYZ", False), ("p2pkh", "^3", False),
+    ("p2tr", "^bc1pqq", False), ("p2tr", "ead$", False, 1 << 19), ("p2tr", "^bc1p.*zzz", False),
+    ("p2pkh", "abc$", False), ("p2pkh", "[0-9]{4}$", False), ("p2pkh", "^1.*XYZ", False),
     # anchored alternations / optional tails: prefixes read off the DFA become digest intervals (lowering.cpp)
     ("p2pkh", "^(1Ca|1Do)", False), ("p2pkh", "^1(Ca|Do)t?x", False), ("p2wpkh", "^bc1q(aa|zz)", False),
-    ("ethereum", "^0x(de|be)a", False), ("p2tr", "^bc1p(qq|pp)", False), ("p2sh-p2wpkh", "^(3Ab|3Cd)$", False),
+    ("ethereum", "^0x(de|be)a", False), ("p2tr", "^bc1p(qq|pp)", False),
     # Ethereum case-sensitive patterns: the case-folded DFA runs first, the EIP-55 hash only for keys it accepts
     ("ethereum", "[A-F]{3}$", False), ("ethereum", "(?-i:aB)", False), ("ethereum", "e$", False), ("ethereum", "Ab|cD", False),
-    # literal suffixes: tested on the Bech32 checksum bits / the last digest bits before any DFA step (vg_dfa_dev::chk_mask)
+    # literal suffixes: tested on the Bech32 checksum bits / the last digest bits / the Base58 residue before any DFA step
     ("p2wpkh", "qq$", False), ("p2wpkh", "ZQ$", True), ("p2tr", "7$", False), ("ethereum", "1f$", False), ("ethereum", "AB$", True),
     ("ethereum", "AB$", False), ("ethereum", "07$", False),
-])
-def test_scan_match_sets_small(small_runner, fmt, pat, ci):
-    _check_scan(small_runner, fmt, pat, 2**64, 1 << 18, ci)
+    ("p2pkh", "at$", False), ("p2pkh", "AT$", True), ("p2sh-p2wpkh", "Zz$", False), ("p2pkh-uncompressed", "7$", False),
+    # a prefix and a tail: interval prefilter + device DFA on the survivors (vg_matcher_dev::confirm_dfa)
+    ("p2pkh", "^1C.*z$", False), ("p2wpkh", "^bc1qa.*zz$", False), ("ethereum", "^0xAb", False), ("p2sh-p2wpkh", "^3A.*[0-9]$", False),
+]
+
+
+@pytest.mark.parametrize("case", SMALL_CASES, ids=lambda c: "%s-%s%s" % (c[0], c[1], "-i" if c[2] else ""))
+def test_scan_match_sets_small(small_runner, case):
+    fmt, pat, ci = case[:3]
+    n = case[3] if len(case) > 3 else 1 << 18
+    res = _check_scan(small_runner, fmt, pat, 2**64, n, ci)
+    assert len(res.matches) > 0, "vacuous case: resize it"
+
+
+@pytest.mark.parametrize("fmt,pat", [("p2tr", "^bc1q"), ("p2pkh", "^3"), ("p2sh-p2wpkh", "^(3Ab|3Cd)$"), ("p2wpkh", "^1"), ("ethereum", "^0xg")])
+def test_scan_patterns_that_cannot_match(small_runner, fmt, pat):
+    """Patterns no address of the format can match: the lowering says so ("none") and the scan reports the range as scanned."""
+    res = _check_scan(small_runner, fmt, pat, 2**64, 1 << 16)
+    assert res.matches == [] and res.operations == 1 << 16
+    assert small_runner.matcher_kind() == "none"
 
 
 def test_scan_edges(small_runner):
@@ -136,13 +155,16 @@ def test_scan_edges(small_runner):
     res = _scan(small_runner, "p2pkh", ".", 0, 3000)
     assert [int(m.hex, 16) for m in res.matches] == list(range(1, 3000)) and res.operations == 2999
     # tail of the group: stops at n-1
-    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=0, start=N - 500, end=None)
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=vg.UNLIMITED, start=N - 500, end=None)
     res = vg.scan_gpu_with_runner(vg.Pattern("^1"), cfg, None, None, small_runner)
     assert [int(m.hex, 16) for m in res.matches] == list(range(N - 500, N)) and res.operations == 500
     # count: first `count` matches in ascending key order (src/gpu.rs:1095-1104)
     res = _scan(small_runner, "p2pkh", "^1A", 1, 1 << 16, count=3)
     keys, _, _ = oracle.scan_range("p2pkh", "^1A", 1, 1 << 16)
     assert [int(m.hex, 16) for m in res.matches] == keys[:3]
+    # count == 0: the library stops before the first window (src/gpu.rs:981-996); only the CLI maps 0 to "no limit" (src/lib.rs:524)
+    res = _scan(small_runner, "p2pkh", "^1A", 1, 1 << 16, count=0)
+    assert list(res.matches) == [] and res.operations == 0
     # single key range, ragged end
     res = _scan(small_runner, "p2pkh", ".", 77, 1)
     assert [int(m.hex, 16) for m in res.matches] == [77]
@@ -198,6 +220,63 @@ def test_config_c1_full_match_set(runner):
     assert all(m.address.startswith("1Cat") for m in res.matches)
 
 
+def _verify_hits(fmt, pat, res, start, n, ci=False):
+    """Soundness of a scan too large for a full oracle pass: ascending unique keys inside the range, and every reported hit
+    re-derived by the oracle (address, WIF) and matched by the oracle's regex."""
+    keys = [int(m.hex, 16) for m in res.matches]
+    assert keys == sorted(set(keys)) and all(start <= k < start + n for k in keys)
+    assert res.operations == n
+    for m in res.matches:
+        a, w, _ = oracle.address(fmt, int(m.hex, 16))
+        assert (a, w) == (m.address, m.wif) and oracle.regex_match(pat, a, ci), m
+    return keys
+
+
+def test_config_c2_catdog_planted(runner):
+    """BASELINE.json config C2: P2PKH ^1CatDog (hash160 interval path) over 2^34 keys from 2^64. The pattern itself expects
+    ~1 hit, so completeness is shown with planted keys: the 8-character prefixes of three keys of the range, as an alternation
+    (lowered to intervals from the DFA), must each be found; every reported hit is re-derived by the oracle; the
+    oracle-scanned head of the range is equal."""
+    S, n = 2**64, 1 << 34
+    res = _scan(runner, "p2pkh", "^1CatDog", S, n)
+    assert runner.matcher_kind() == "intervals"
+    keys = _verify_hits("p2pkh", "^1CatDog", res, S, n)
+    want, _, _ = oracle.scan_range("p2pkh", "^1CatDog", S, 1 << 20)
+    assert [k for k in keys if k < S + (1 << 20)] == want
+    planted = [S + 12345, S + n // 3, S + n - 7]
+    pat = "^(" + "|".join(oracle.address("p2pkh", k)[0][:8] for k in planted) + ")"
+    res = _scan(runner, "p2pkh", pat, S, n)
+    assert runner.matcher_kind() == "intervals"
+    keys = _verify_hits("p2pkh", pat, res, S, n)
+    assert all(k in keys for k in planted), "planted keys missing"
+
+
+def test_config_c3_p2wpkh_dead_suffix_full_match_set(runner):
+    """BASELINE.json config C3: P2WPKH dead$ (on-GPU Bech32 + shared-memory DFA) — full match set over 2^24 keys from 2^64
+    against the oracle (probability 2^-20 per key: ~16 hits, so the comparison is not vacuous)."""
+    res = _check_scan(runner, "p2wpkh", "dead$", 2**64, 1 << 24)
+    assert len(res.matches) > 0 and all(m.address.endswith("dead") for m in res.matches)
+    assert runner.matcher_kind() == "dfa"
+
+
+def test_config_c4_ethereum_dead_prefix_full_match_set(runner):
+    """BASELINE.json config C4: Ethereum ^0xdead (uncompressed key + Keccak-256; the EIP-55 case of the four letters must come
+    out lower-case, a 1/16 sub-filter) — full match set over 2^24 keys from 2^64 against the oracle."""
+    res = _check_scan(runner, "ethereum", "^0xdead", 2**64, 1 << 24)
+    assert len(res.matches) > 0 and all(m.address.startswith("0xdead") for m in res.matches)
+
+
+def test_config_c5_exact_address_planted(runner):
+    """BASELINE.json config C5 shape: exact-address match over a 2^35-key window from 2^65, the planted key at 0.83 of the
+    window: exactly that key comes back and every key of the window is counted (the 2^40 window: test_full_size_configs)."""
+    start, n = 2**65, 1 << 35
+    off = int(0.83 * n)
+    addr = oracle.address("p2pkh", start + off)[0]
+    res = _scan(runner, "p2pkh", "^" + addr + "$", start, n)
+    assert [int(m.hex, 16) for m in res.matches] == [start + off] and res.matches[0].address == addr
+    assert res.operations == n and runner.matcher_kind() == "exact"
+
+
 def test_sharded_scan_equals_single(runner):
     """Two shard contexts (as two torchrun ranks would hold) cover the range disjointly: union == single-context set."""
     start, n = 2**64, runner.batch_size * 4 + 999
@@ -224,25 +303,89 @@ def test_stop_flag_and_progress(small_runner):
         seen.append(k)
         if len(seen) == 3:
             stop.set()
-    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=0, start=2**64, end=2**64 + (1 << 30))
+    cfg = vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=vg.UNLIMITED, start=2**64, end=2**64 + (1 << 30))
     res = vg.scan_gpu_with_runner(vg.Pattern("^1CatDogs"), cfg, cb, stop, small_runner)
     assert seen == sorted(seen) and len(seen) >= 3
     assert res.operations < (1 << 30)
 
 
-def test_multi_device_context_equals_single(runner):
-    """One context over two GPUs (lanes on different devices, hits merged on the host) == the single-GPU set."""
+def _n_gpus():
     from vgen_b200 import _cabi
-    if _cabi.lib().vgen_cuda_device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    start, n = 2**64, runner.batch_size * 5 + 4321
+    return int(_cabi.lib().vgen_cuda_device_count())
+
+
+# device lists of one context. [0, 0] drives the same GPU as two "devices" (two host threads, four lanes): the multi-device
+# machinery — one host thread per device, hits merged in window order on the calling thread — runs on a 1-GPU box too.
+MULTI = [[0, 0], [0, 1], [0, 1, 2, 3], [0, 1, 2, 3, 4, 5, 6, 7]]
+
+
+@pytest.mark.parametrize("devs", MULTI, ids=lambda d: "x".join(map(str, d)))
+def test_multi_device_context_equals_single(runner, devs):
+    """One context over several GPUs (one host thread per device, hits merged on the host) == the single-GPU set:
+    the path `vgen --devices 0,1,...` and the Rust binding use."""
+    if max(devs) >= _n_gpus():
+        pytest.skip("needs %d GPUs" % (max(devs) + 1))
+    start, n = 2**64, runner.batch_size * (2 * len(devs) + 3) + 4321
     single = _scan(runner, "p2pkh", "^1Ca", start, n)
-    r2 = vg.GpuRunner(devices=[0, 1])
+    rm = vg.GpuRunner(devices=devs)
     try:
-        both = _scan(r2, "p2pkh", "^1Ca", start, n)
+        assert rm.lane_count() == 2 * len(devs) and rm.stats()["devices"] == len(devs)
+        multi = _scan(rm, "p2pkh", "^1Ca", start, n)
+        assert [m.hex for m in multi.matches] == [m.hex for m in single.matches] and multi.operations == n
+        # a hit limit: the first `count` matches in ascending key order, whichever device found them
+        few = _scan(rm, "p2pkh", "^1Ca", start, n, count=7)
+        assert [m.hex for m in few.matches] == [m.hex for m in single.matches][:7]
+        # a DFA pattern and a dense one through the same context
+        _check_scan(rm, "p2wpkh", "qq$", 2**64, 1 << 18)
+        res = _scan(rm, "p2pkh", ".", 5, 5000)
+        assert [int(m.hex, 16) for m in res.matches] == list(range(5, 5005))
     finally:
-        r2.close()
-    assert [m.hex for m in both.matches] == [m.hex for m in single.matches] and both.operations == n
+        rm.close()
+
+
+def test_failed_device_windows_are_requeued(runner, monkeypatch):
+    """SURVEY.md section 5, failure row: a device whose CUDA call fails drops out of the scan, the windows it had in flight
+    and the rest of its lanes' windows are taken over by the surviving devices, and the result is still the exact set
+    (the reference falls back to the CPU scanner instead, src/lib.rs:727-746,1185-1197; north_star forbids that).
+    VGEN_FAULT_INJECT=<device index>:<n> makes the n-th window issue of that device return an error."""
+    devs = [0, 1] if _n_gpus() >= 2 else [0, 0]
+    start, n = 2**64, runner.batch_size * 9 + 777
+    single = _scan(runner, "p2pkh", "^1Ca", start, n)
+    rm = vg.GpuRunner(devices=devs)
+    try:
+        monkeypatch.setenv("VGEN_FAULT_INJECT", "1:2")          # device 1 fails at its third window
+        res = _scan(rm, "p2pkh", "^1Ca", start, n)
+        st = rm.stats()
+        assert st["failed_devices"] == 1 and st["requeued_windows"] >= 1, st
+        assert [m.hex for m in res.matches] == [m.hex for m in single.matches] and res.operations == n
+        monkeypatch.delenv("VGEN_FAULT_INJECT")
+        # the device stays out; later scans of the context run on the survivor alone and stay exact
+        res = _scan(rm, "p2pkh", "^1Ca", start + 99, n)
+        keys, _, _ = oracle.scan_range("p2pkh", "^1Ca", start + 99, 1 << 20)
+        assert [int(m.hex, 16) for m in res.matches if int(m.hex, 16) < start + 99 + (1 << 20)] == keys and res.operations == n
+        assert rm.stats()["failed_devices"] == 1
+        # when the last device fails too, the scan fails loudly: there is no CPU fallback
+        monkeypatch.setenv("VGEN_FAULT_INJECT", "0:1")
+        with pytest.raises(Exception, match="no device left"):
+            _scan(rm, "p2pkh", "^1Ca", start, n)
+    finally:
+        rm.close()
+
+
+def test_hit_buffer_overflow_is_rescanned(monkeypatch):
+    """Hit buffers hold fewer records than a window has keys; a window that reports more hits than fit is re-run in pieces of a
+    smaller ramp level (engine.cpp harvest). Forced here with a tiny buffer (VGEN_HIT_CAP) and a pattern that matches ~15 % of
+    the keys; the match set must still equal the oracle's."""
+    monkeypatch.setenv("VGEN_HIT_CAP", str(1 << 18))
+    r = vg.GpuRunner(8 * 262144)                       # 2,097,152 keys per window, 262,144 hit records per slot
+    try:
+        assert r.stats()["hit_cap"] == 1 << 18 and r.batch_size == 8 * 262144
+        n = 2 * r.batch_size + 1000
+        res = _check_scan(r, "p2pkh", "[1-9]$", 2**64, n)
+        assert len(res.matches) > 2 * (1 << 18)
+        assert r.stats()["overflow_rescans"] >= 2
+    finally:
+        r.close()
 
 
 def test_two_lanes_per_gpu_cover_the_range_once(runner):
@@ -288,6 +431,6 @@ def test_dispatch_await_frames(small_runner):
     xs, _ = r.await_result_p2tr(0)
     for i in (0, 1, 2, 1000, r.batch_size - 1):
         assert int.from_bytes(xs[i], "big") == oracle.pubkey(a + i)[0]
-    res = vg.scan_gpu_p2tr_with_runner(vg.Pattern("^bc1pqq"), vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=0, start=a, end=a + (1 << 16)), None, None, r)
+    res = vg.scan_gpu_p2tr_with_runner(vg.Pattern("^bc1pqq"), vg.ScanConfig(format=vg.AddressFormat.P2pkh, count=vg.UNLIMITED, start=a, end=a + (1 << 16)), None, None, r)
     keys, _, _ = oracle.scan_range("p2tr", "^bc1pqq", a, (1 << 16) + 1)
     assert [int(m.hex, 16) for m in res.matches] == keys and all(m.format == vg.AddressFormat.P2tr for m in res.matches)

@@ -14,7 +14,7 @@ for devs in ([0], [0, 0], [0, 0, 0]):
     for it in range(3):
         a = (1 << 64) + (1 << 50) + it * span
         t0 = time.perf_counter()
-        res = vg.scan_gpu_with_runner(pat, vg.ScanConfig(format=fmt, count=0, start=a, end=a + span - 1), None, None, r)
+        res = vg.scan_gpu_with_runner(pat, vg.ScanConfig(format=fmt, count=vg.UNLIMITED, start=a, end=a + span - 1), None, None, r)
         dt = time.perf_counter() - t0
         best = max(best, res.operations / dt / 1e6)
     print("lanes on GPU0: %d  window %d keys  best %.0f Mkeys/s  (hits %d)" % (len(devs), r.batch_size, best, len(res.matches)), flush=True)

@@ -5,10 +5,10 @@ Python host mirror of the reference's crate-root re-exports (src/lib.rs:9-12) ov
 every scan entry point needs the built library and a B200."""
 from . import _cabi
 from .address import AddressFormat, GeneratedAddress, address_from_digest, wif_from_key
-from .gpu import DEFAULT_BATCH_SIZE, GpuBackend, GpuRunner, StopFlag, plan_windows, scan_gpu, scan_gpu_p2tr, scan_gpu_p2tr_with_runner, scan_gpu_with_runner
+from .gpu import DEFAULT_BATCH_SIZE, UNLIMITED, DigestBatch, GpuBackend, GpuRunner, StopFlag, plan_windows, scan_gpu, scan_gpu_p2tr, scan_gpu_p2tr_with_runner, scan_gpu_with_runner
 from .pattern import Pattern
 from .scanner import ScanConfig, ScanResult
 
 __all__ = ["AddressFormat", "GeneratedAddress", "GpuBackend", "GpuRunner", "StopFlag", "Pattern", "ScanConfig", "ScanResult",
-           "scan_gpu", "scan_gpu_with_runner", "scan_gpu_p2tr", "scan_gpu_p2tr_with_runner", "plan_windows", "DEFAULT_BATCH_SIZE", "address_from_digest", "wif_from_key"]
+           "scan_gpu", "scan_gpu_with_runner", "scan_gpu_p2tr", "scan_gpu_p2tr_with_runner", "plan_windows", "DEFAULT_BATCH_SIZE", "UNLIMITED", "DigestBatch", "address_from_digest", "wif_from_key"]
 __version__ = "0.1.0"

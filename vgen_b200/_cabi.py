@@ -42,6 +42,7 @@ SYMBOLS = {
     "vgen_cuda_window_keys": (C.c_uint64, [C.c_void_p]),
     "vgen_cuda_lane_count": (C.c_int, [C.c_void_p]),
     "vgen_cuda_tap_bits": (C.c_int, [C.c_void_p]),
+    "vgen_cuda_stats": (None, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "vgen_cuda_io_bytes": (None, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "vgen_format_address": (C.c_int, [C.c_int, C.c_char_p, C.c_char_p, C.c_size_t]),
     "vgen_format_wif": (C.c_int, [C.c_int, C.c_char_p, C.c_char_p, C.c_size_t]),

@@ -176,10 +176,18 @@ int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t
     if (!ctx->engine.bench_resident(vg::U256::from_be(start_be), n_windows, *ms, *keys, *launches, err)) return fail(ctx, VGEN_ERR_CUDA, err);
     return VGEN_OK;
 }
-uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.launches : 0; }
+uint64_t vgen_cuda_launch_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.launches.load() : 0; }
 void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h) {
-    if (h2d) *h2d = ctx ? ctx->engine.h2d_bytes : 0;
-    if (d2h) *d2h = ctx ? ctx->engine.d2h_bytes : 0;
+    if (h2d) *h2d = ctx ? ctx->engine.h2d_bytes.load() : 0;
+    if (d2h) *d2h = ctx ? ctx->engine.d2h_bytes.load() : 0;
+}
+void vgen_cuda_stats(const vgen_ctx *ctx, uint64_t out[8]) {
+    if (!out) return;
+    memset(out, 0, 8 * sizeof(uint64_t));
+    if (!ctx) return;
+    const vg::Engine &e = ctx->engine;
+    out[0] = (uint64_t)e.n_devices(); out[1] = (uint64_t)e.n_failed_devices(); out[2] = e.requeued_windows.load();
+    out[3] = e.overflow_rescans.load(); out[4] = e.hit_cap(); out[5] = e.pool_threads();
 }
 int vgen_cuda_lane_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.n_lanes() : 0; }
 int vgen_cuda_tap_bits(const vgen_ctx *ctx) { return ctx ? (int)ctx->engine.tap_bits() : 0; }
@@ -269,6 +277,7 @@ int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, si
         s += ";exact=";
         for (int i = 0; i < lp.dev.exact_words * 4; i++) { snprintf(buf, sizeof buf, "%02x", (lp.dev.exact[i / 4] >> (8 * (i % 4))) & 0xff); s += buf; }
     }
+    if (lp.dev.confirm_dfa) s += ";confirm=dfa";       // the device runs the DFA on the keys that pass the prefilter
     if (lp.dev.kind == VG_MATCH_DFA && lp.dev.dfa.chk_mask != 0) {      // literal-suffix test ahead of the DFA (scan_types.h)
         snprintf(buf, sizeof buf, ";suffix=%08x:%08x", lp.dev.dfa.chk_mask, lp.dev.dfa.chk_value);
         s += buf;

@@ -259,6 +259,11 @@ static bool intervals_from_prefixes(int format, const std::vector<std::string> &
         out.dev.lo_hi[i][0] = (uint32_t)(merged[i].first >> 32); out.dev.lo_hi[i][1] = (uint32_t)merged[i].first;
         out.dev.lo_hi[i][2] = (uint32_t)(merged[i].second >> 32); out.dev.lo_hi[i][3] = (uint32_t)merged[i].second;
     }
+    // The intervals are only a prefilter when something follows the prefix (^1C.*z$, ^bc1qa.*zz$) or when the pattern tells
+    // a-f from A-F (Ethereum ^0xAb: the intervals ignore the EIP-55 case): the device then runs the staged DFA on the
+    // survivors, so that only real matches cross PCIe. Without it every prefix candidate (1.3 M records per 77.6 M-key window
+    // for a 2-character Base58 prefix) would be re-encoded on the host and the scan would be host-bound.
+    if (!decides || (format == VG_FMT_ETHEREUM && (out.dev.dfa.flags & 1u))) out.dev.confirm_dfa = 1;
     return true;
 }
 

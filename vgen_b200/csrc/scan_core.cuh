@@ -158,6 +158,17 @@ VG_DEV void vg_process_pair(const vg_scan_params &P, const vg_dfa_view &dv, fe &
 #ifndef VG_SYNC_ITER
 #define VG_SYNC_ITER 4
 #endif
+// VG_PHASE_SPLIT = 1: the two halves of the CTA (warps 0-3 / 4-7, i.e. one warp of each half on every SM sub-partition) meet
+// the barrier at DIFFERENT points of the step: the first half at the top (before the two inverse-peeling multiplications), the
+// second half in the middle (after the second affine addition, before its hash). The halves then run the same code about half
+// a step apart: while one half is in the multiplier-bound EC stretch (carry-chained IMAD.WIDE, half rate, ALU pipe idle) the
+// other is in the ALU-bound hash stretch, and they still share instruction fetches one stretch later.
+#ifndef VG_PHASE_SPLIT
+#define VG_PHASE_SPLIT 0
+#endif
+#if !defined(VG_HOST_EMU)
+#define VG_CTA_BARRIER() asm volatile("bar.sync 0;" ::: "memory")
+#endif
 
 #define VG_LOAD_FE(dst, base, stride_words) { VG_UNROLL for (int _l = 0; _l < 8; _l++) (dst).v[_l] = (base)[(size_t)_l * (stride_words)]; }
 #define VG_STORE_FE(base, stride_words, src) { VG_UNROLL for (int _l = 0; _l < 8; _l++) (base)[(size_t)_l * (stride_words)] = (src).v[_l]; }
@@ -190,10 +201,17 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const
     fe_inv(inv, prod);
 
     const unsigned long long idx_c = (unsigned long long)tid * (2ull * H) + H;
+#if VG_SYNC_ITER && VG_PHASE_SPLIT && !defined(VG_HOST_EMU)
+    const bool late_half = threadIdx.x >= blockDim.x / 2;
+#endif
     // backward pass: peel one inverse per step, derive both neighbours, hash, match
     for (uint32_t i = H; i >= 1; i--) {
 #if VG_SYNC_ITER && !defined(VG_HOST_EMU)
+  #if VG_PHASE_SPLIT
+        if ((i % VG_SYNC_ITER) == 0 && !late_half) VG_CTA_BARRIER();
+  #else
         if ((i % VG_SYNC_ITER) == 0) __syncthreads();
+  #endif
 #endif
         const uint32_t *g = gtab + (size_t)(i - 1) * 16;
         fe gx, gy, pre, inv_i;
@@ -225,6 +243,9 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const
                     if (side) fe_neg(by, gy); else by = gy;
                     affine_add_inv(x3, y3, cx, cy, gx, by, inv_i);
                 }
+#if VG_SYNC_ITER && VG_PHASE_SPLIT && !defined(VG_HOST_EMU)
+                if (side == 1 && (i % VG_SYNC_ITER) == 0 && late_half) VG_CTA_BARRIER();
+#endif
                 vg_process_point<FMT, MODE>(P, dv, x3, y3, idx, !degenerate);
             }
         }
@@ -247,15 +268,32 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const
 }
 
 // ---- cold-path thread bodies ----
-// pow2[i] = 2^i * G for i = 0..255, built serially by one thread at context creation
-VG_DEV void vg_build_pow2(uint32_t *pow2, const uint32_t gxy[16]) {
-    gej_t p; fe x, y;
-    VG_UNROLL for (int l = 0; l < 8; l++) { x.v[l] = gxy[l]; y.v[l] = gxy[8 + l]; }
+// pow2[i] = 2^i * G for i = 0..255, built by one thread at context creation: 255 Jacobian doublings, then ONE field
+// inversion for all 256 points (Montgomery's trick over the Z coordinates) instead of one per point (round 1: 25.5 ms of
+// serial kernel time per lane; now ~4 k field multiplications, once per device). scratch: 256 * 32 words.
+VG_DEV void vg_build_pow2(uint32_t *pow2, const uint32_t gxy[16], uint32_t *scratch) {
+    gej_t p;
+    VG_UNROLL for (int l = 0; l < 8; l++) { p.x.v[l] = gxy[l]; p.y.v[l] = gxy[8 + l]; }
+    fe_set_one(p.z); p.inf = false;
+    fe run; fe_set_one(run);
     for (int i = 0; i < 256; i++) {
-        for (int l = 0; l < 8; l++) { pow2[i * 16 + l] = x.v[l]; pow2[i * 16 + 8 + l] = y.v[l]; }
-        p.x = x; p.y = y; fe_set_one(p.z); p.inf = false;
-        gej_t d; gej_double(d, p);
-        gej_to_affine(x, y, d);
+        uint32_t *o = scratch + i * 32;
+        fe_mul(run, run, p.z);
+        for (int l = 0; l < 8; l++) { o[l] = p.x.v[l]; o[8 + l] = p.y.v[l]; o[16 + l] = p.z.v[l]; o[24 + l] = run.v[l]; }
+        gej_t d; gej_double(d, p); p = d;
+    }
+    fe inv;
+    fe_inv(inv, run);
+    for (int i = 255; i >= 0; i--) {
+        const uint32_t *o = scratch + i * 32;
+        fe X, Y, Z, zi, zi2, zi3;
+        for (int l = 0; l < 8; l++) { X.v[l] = o[l]; Y.v[l] = o[8 + l]; Z.v[l] = o[16 + l]; }
+        if (i > 0) { fe pre; for (int l = 0; l < 8; l++) pre.v[l] = o[l - 8]; fe_mul(zi, inv, pre); fe_mul(inv, inv, Z); }
+        else zi = inv;
+        fe_sqr(zi2, zi); fe_mul(zi3, zi2, zi);
+        fe_mul(X, X, zi2); fe_mul(Y, Y, zi3);
+        fe_canon(X); fe_canon(Y);
+        for (int l = 0; l < 8; l++) { pow2[i * 16 + l] = X.v[l]; pow2[i * 16 + 8 + l] = Y.v[l]; }
     }
 }
 // affine point of scalar base + mul*tid + add, stored limb-major at column tid of out[16][n]; zeros if invalid

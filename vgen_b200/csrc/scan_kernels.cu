@@ -13,7 +13,7 @@ __global__ void k_build_pow2(uint32_t *pow2) {
     const uint32_t gxy[16] = {
         0x16F81798u, 0x59F2815Bu, 0x2DCE28D9u, 0x029BFCDBu, 0xCE870B07u, 0x55A06295u, 0xF9DCBBACu, 0x79BE667Eu,
         0xFB10D4B8u, 0x9C47D08Fu, 0xA6855419u, 0xFD17B448u, 0x0E1108A8u, 0x5DA4FBFCu, 0x26A3C465u, 0x483ADA77u};
-    if (blockIdx.x == 0 && threadIdx.x == 0) vg_build_pow2(pow2, gxy);
+    if (blockIdx.x == 0 && threadIdx.x == 0) vg_build_pow2(pow2, gxy, pow2 + VG_GTABLE_POW2_WORDS);      // scratch: the win8 area, built afterwards
 }
 
 // out[16][n] (limb-major) column t = (base + t*step) * G; all-zero column when the scalar is invalid

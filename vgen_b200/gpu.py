@@ -1,6 +1,7 @@
 """GpuRunner / scan_gpu_with_runner / scan_gpu — the reference's GPU scan surface (src/gpu.rs:18-63,128-136,138,
 535-665,920-1166) over libvgen_cuda.so. Same names and argument meaning; the wgpu backends are replaced by CUDA, and
 there is no CPU fallback: if the library or a B200 is missing, construction raises."""
+import collections.abc
 import ctypes as C
 import enum
 import itertools
@@ -14,6 +15,7 @@ from .pattern import Pattern
 from .scanner import MatchList, ScanConfig, ScanResult
 
 DEFAULT_BATCH_SIZE = 512 * 1024          # src/gpu.rs:83; here only a keys-per-launch hint (0 = fill the GPU)
+UNLIMITED = (1 << 64) - 1                # usize::MAX: what the reference's CLI turns `--count 0` into (src/lib.rs:524)
 SECP256K1_N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
 
 
@@ -85,33 +87,38 @@ class GpuRunner:
         if rc != 0:
             raise _cabi.VgenError(rc, (self._lib.vgen_cuda_last_error(self._ctx) or b"").decode())
 
-    # -- reference-shaped batch API (generate_batch, src/gpu.rs:660-665): hash160 of n sequential keys
+    # -- reference-shaped batch API (generate_batch, src/gpu.rs:660-665): hash160 of n sequential keys.
+    # The frame size of this API is independent of the scan window (which defaults to 77.6 M keys here): `frame_size` keys,
+    # DEFAULT_BATCH_SIZE unless the runner was created with a smaller batch. Results come back as ONE buffer (DigestBatch).
+    @property
+    def frame_size(self):
+        return min(self.batch_size, DEFAULT_BATCH_SIZE)
+
     def generate_batch(self, start_key, n=None):
-        n = self.batch_size if n is None else int(n)
+        n = self.frame_size if n is None else int(n)
         buf = C.create_string_buffer(20 * n)
         self._check(self._lib.vgen_cuda_hash160_batch(self._ctx, _be(start_key), n, buf))
-        raw = buf.raw
-        return [raw[20 * i:20 * i + 20] for i in range(n)]
+        return DigestBatch(buf.raw, 20)
 
     # -- the reference's two-frame dispatch / await API (src/gpu.rs:535-658, 667-807). A frame is computed by a worker thread
     # (ctypes releases the GIL); frames of one runner are serialised by a lock because a context runs one job at a time.
-    def _dispatch(self, kind, start_key, frame_index):
+    def _dispatch(self, kind, start_key, frame_index, n=None):
         if frame_index not in (0, 1):
             raise IndexError("frame_index must be 0 or 1")          # two frames in flight (src/gpu.rs:399)
         if not hasattr(self, "_frames"):
             self._frames, self._frame_lock = {}, threading.Lock()
+        n = self.frame_size if n is None else int(n)
         box = {}
 
         def work():
             try:
                 with self._frame_lock:
                     if kind == "p2tr":
-                        buf = C.create_string_buffer(32 * self.batch_size)
-                        self._check(self._lib.vgen_cuda_digest_batch(self._ctx, 6, _be(start_key), self.batch_size, buf, 32))
-                        raw = buf.raw
-                        box["out"] = [raw[32 * i:32 * i + 32] for i in range(self.batch_size)]
+                        buf = C.create_string_buffer(32 * n)
+                        self._check(self._lib.vgen_cuda_digest_batch(self._ctx, 6, _be(start_key), n, buf, 32))
+                        box["out"] = DigestBatch(buf.raw, 32)
                     else:
-                        box["out"] = self.generate_batch(start_key, self.batch_size)
+                        box["out"] = self.generate_batch(start_key, n)
             except Exception as e:                                   # surfaced by await_result
                 box["err"] = e
         t = threading.Thread(target=work, daemon=True)
@@ -125,20 +132,20 @@ class GpuRunner:
             raise box["err"]
         return box["out"], start
 
-    def dispatch(self, start_key, frame_index=0):
-        self._dispatch("h160", start_key, frame_index)
+    def dispatch(self, start_key, frame_index=0, n=None):
+        self._dispatch("h160", start_key, frame_index, n)
 
     def await_result(self, frame_index=0):
-        """([hash160 bytes] * batch_size, start_key_bytes) of the frame (src/gpu.rs:602-658)."""
+        """(DigestBatch of `frame_size` hash160s, start_key_bytes) of the frame (src/gpu.rs:602-658)."""
         return self._await("h160", frame_index)
 
     dispatch_batch_hash = dispatch                                   # src/gpu.rs:809: same result through the batch-inversion kernel
 
-    def dispatch_p2tr(self, start_key, frame_index=0):
-        self._dispatch("p2tr", start_key, frame_index)
+    def dispatch_p2tr(self, start_key, frame_index=0, n=None):
+        self._dispatch("p2tr", start_key, frame_index, n)
 
     def await_result_p2tr(self, frame_index=0):
-        """([32-byte x-only even-Y internal key] * batch_size, start_key_bytes): untweaked, as src/gpu.rs:750-807."""
+        """(DigestBatch of 32-byte x-only even-Y internal keys, start_key_bytes): untweaked, as src/gpu.rs:750-807."""
         return self._await("p2tr", frame_index)
 
     def digest_batch(self, fmt, start_key, n):
@@ -165,6 +172,12 @@ class GpuRunner:
 
     def launch_count(self):
         return int(self._lib.vgen_cuda_launch_count(self._ctx))
+
+    def stats(self):
+        """dict of the context's counters (vgen_cuda_stats): devices, failed_devices, requeued_windows, overflow_rescans, hit_cap, confirm_threads."""
+        a = (C.c_uint64 * 8)()
+        self._lib.vgen_cuda_stats(self._ctx, a)
+        return dict(devices=a[0], failed_devices=a[1], requeued_windows=a[2], overflow_rescans=a[3], hit_cap=a[4], confirm_threads=a[5])
 
     def io_bytes(self):
         a, b = C.c_uint64(0), C.c_uint64(0)
@@ -246,6 +259,35 @@ def plan_windows(start, end, global_lanes, lane, sm_count=148, keys_per_launch_h
     return [(int.from_bytes(raw[32 * i:32 * i + 32], "big"), int(lens[i])) for i in range(n)]
 
 
+class DigestBatch(collections.abc.Sequence):
+    """Digests of consecutive keys as ONE bytes object (`raw`, `stride` bytes per key) with sequence access to the per-key
+    digests: what the reference returns as Vec<[u8; 20]> (src/gpu.rs:644-650) without building one Python object per key."""
+
+    def __init__(self, raw, stride):
+        self.raw, self.stride = raw, int(stride)
+
+    def __len__(self):
+        return len(self.raw) // self.stride
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        n = len(self)
+        if i < 0:
+            i += n
+        if not 0 <= i < n:
+            raise IndexError(i)
+        return self.raw[self.stride * i:self.stride * (i + 1)]
+
+    def __bytes__(self):
+        return self.raw
+
+    def __eq__(self, other):
+        if isinstance(other, DigestBatch):
+            return self.raw == other.raw and self.stride == other.stride
+        return list(self) == list(other)
+
+
 class StopFlag:
     """Arc<AtomicBool> of the reference (src/gpu.rs:924): a 32-bit flag the library polls after every window."""
 
@@ -264,7 +306,10 @@ class StopFlag:
 
 def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
     """src/gpu.rs:920-1125: sequential scan from config.start (or a random valid key) to config.end, first `count`
-    matches in ascending key order. operations = exact valid keys tested (Appendix A of SURVEY.md)."""
+    matches in ascending key order. operations = exact valid keys tested (Appendix A of SURVEY.md).
+    `count` has the library's meaning: the scan ends once `count` matches are found, so count == 0 returns at once with no
+    matches and no operations (src/gpu.rs:981-996: `found >= config.count` holds before the first dispatch); "no limit" is
+    UNLIMITED = usize::MAX, which is what the reference's CLI substitutes for `--count 0` (src/lib.rs:524)."""
     if not isinstance(pattern, Pattern):
         pattern = Pattern(pattern)
     fmt = AddressFormat.parse(config.format)
@@ -278,11 +323,13 @@ def scan_gpu_with_runner(pattern, config, progress_cb, stop, runner):
     runner.set_pattern(pattern, fmt)
     t0 = time.perf_counter()
     count = int(config.count)
+    if count <= 0:
+        return ScanResult(matches=MatchList(b"", 0, fmt), operations=0, elapsed_secs=time.perf_counter() - t0)
+    max_hits = 0 if count >= UNLIMITED else count                         # C ABI: max_hits 0 = unlimited
     # first call with a 1-record buffer: the confirmed hits stay in the context and are formatted in bulk below
-    _, scanned = runner.scan_raw(start, end, max_hits=count, stop=stop._ptr() if stop is not None else None, progress=progress_cb,
+    _, scanned = runner.scan_raw(start, end, max_hits=max_hits, stop=stop._ptr() if stop is not None else None, progress=progress_cb,
                                  hits_cap=1, fetch_all=False)
     total = int(runner._lib.vgen_cuda_scan_total_hits(runner._ctx))
-    elapsed = time.perf_counter() - t0
     text, got = runner.fetch_text(total)
     matches = MatchList(text, got, fmt)
     elapsed = time.perf_counter() - t0

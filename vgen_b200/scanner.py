@@ -10,7 +10,7 @@ from .address import AddressFormat, GeneratedAddress
 @dataclass
 class ScanConfig:
     format: AddressFormat = AddressFormat.P2pkh
-    count: int = 1                          # 0 = unlimited (src/lib.rs:524 maps 0 -> usize::MAX)
+    count: int = 1                          # matches wanted; vgen_b200.UNLIMITED (usize::MAX) = no limit, which is what the CLI turns 0 into (src/lib.rs:524)
     threads: Optional[int] = None
     gpu_batch_size: Optional[int] = None
     cpu_batch_size: Optional[int] = None
