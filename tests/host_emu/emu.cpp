@@ -90,6 +90,17 @@ int emu_confirm_chk(int fmt, const uint32_t *dg, const uint16_t *table, const ui
     dv.poly = fmt == 2 ? tab32 : tab52;
     return fmt == 2 ? vg_confirm<2>(m, dv, dg) : vg_confirm<4>(m, dv, dg);
 }
+// Base58 matcher with the literal-suffix residue prefilter (vg_dfa_dev::b58_mod ...): 13 half-word weights, Barrett constant
+int emu_confirm_b58res(int fmt, const uint32_t *dg, const uint16_t *table, const uint8_t *accept, const uint8_t *sym_class,
+                       uint32_t n_classes, uint32_t start, uint32_t flags, uint32_t mod, uint32_t nvals, const uint32_t *vals,
+                       const uint32_t *w, uint32_t mu_lo, uint32_t mu_hi) {
+    vg_matcher_dev m; memset(&m, 0, sizeof m);
+    m.dfa.n_classes = n_classes; m.dfa.start = start; m.dfa.flags = flags;
+    m.dfa.b58_mod = mod; m.dfa.b58_nvals = nvals; m.dfa.b58_mu_lo = mu_lo; m.dfa.b58_mu_hi = mu_hi;
+    memcpy(m.dfa.b58_vals, vals, 4 * (nvals < 8 ? nvals : 8)); memcpy(m.dfa.b58_w, w, 4 * 13);
+    vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
+    return fmt == 3 ? vg_confirm<3>(m, dv, dg) : vg_confirm<0>(m, dv, dg);
+}
 // Ethereum matcher with the case-folded DFA appended behind the exact one (lowering.cpp): table / accept hold both
 int emu_confirm_eth_fold(const uint32_t *dg, const uint16_t *table, const uint8_t *accept, const uint8_t *sym_class,
                          uint32_t n_classes, uint32_t start, uint32_t flags, uint32_t fold_table, uint32_t fold_accept,

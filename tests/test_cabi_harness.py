@@ -77,11 +77,10 @@ def test_harness_scan_equals_oracle(fmt, fid, pat):
     for h in rec["HIT"]:
         a, w, _ = oracle.address(fmt, int(h[0], 16))
         assert (h[1], h[2]) == (a, w)
-    f = dict(zip(rec["SCANNED"].split()[0::2], rec["SCANNED"].split()[1::2]))          # "n TOTAL t FIRST f ..." after the key
     toks = ("SCANNED " + rec["SCANNED"]).split()
     f = dict(zip(toks[0::2], toks[1::2]))
     assert int(f["SCANNED"]) == ops == int(f["LAST"]) and int(f["TOTAL"]) == len(keys) and int(f["FIRST"]) == 4
-    assert int(f["CALLBACKS"]) >= 2 and f["MONOTONE"] == "1" and f["STOPPED"] == "0"
+    assert int(f["CALLBACKS"]) >= 1 and f["MONOTONE"] == "1" and f["STOPPED"] == "0"          # one callback per window
     assert "regex" in rec["BADPATTERN"].lower() or "pattern" in rec["BADPATTERN"].lower()
     # the frame calls: hash160 of consecutive keys, frame 1 continuing where frame 0 ended; P2TR frame = untweaked x-only keys
     assert bytes.fromhex(rec["FRAME0"]) == oracle.hash160_batch(start, 4096)

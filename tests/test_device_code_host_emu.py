@@ -248,6 +248,50 @@ def test_segwit_checksum_suffix_prefilter(emu, fmt):
         assert n_hit > 0, (fmt, pat)
 
 
+@pytest.mark.parametrize("fmt", ["p2pkh", "p2sh-p2wpkh"])
+def test_base58_literal_suffix_residue_prefilter(emu, fmt):
+    """Literal-suffix patterns on Base58 formats (Cat$): the last k characters are the Base58Check payload mod 58^k, so the device
+    compares that residue (13 multiply-adds + one Barrett reduction, vg_dfa_dev::b58_mod / b58_vals) before the radix
+    conversion and the DFA. The lowering exposes the residues (Pattern.lowering()["residue"]); the verdict must equal the
+    oracle's regex over the address string, for matching and non-matching keys alike."""
+    import vgen_b200 as vg
+    B58 = "123456789ABCDEFGHJKLMNPQRSTUVWXYZabcdefghijkmnopqrstuvwxyz"
+    rng = random.Random(31)
+    F = vg.AddressFormat.parse(fmt)
+    digests = [bytes(rng.randrange(256) for _ in range(20)) for _ in range(3000)]
+    digests += [b"\0" * 20, b"\xff" * 20, b"\0" * 19 + b"\1", b"\0" * 10 + b"\xff" * 10]
+    emu.emu_confirm_b58res.argtypes = [C.c_int, C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p] + [C.c_uint32] * 5 + [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+    full = oracle.address_from_digest(fmt, digests[5])
+    for pat, ci in [("1$", False), ("z$", False), (full[-2:] + "$", False), (full[-3:] + "$", False), (full[-5:] + "$", False),
+                    (full[-2:].swapcase() + "$", True), ("a$", True), ("l$", True), ("o$", True)]:
+        low = vg.Pattern(pat, ci).lowering(F)
+        assert low["kind"] == "dfa" and low["residue"], (pat, low)
+        M, vals = low["residue"][0], list(low["residue"][1:])
+        lit = pat[:-1]
+        assert M == 58 ** len(lit)
+        # every spelling the alphabet has, as a base-58 number
+        import itertools
+        spell = [sorted({c, c.swapcase()} & set(B58)) if ci else [c] for c in lit]
+        want_vals = sorted(sum(B58.index(ch) * 58 ** (len(t) - 1 - i) for i, ch in enumerate(t)) for t in itertools.product(*spell))
+        assert sorted(vals) == want_vals, (pat, vals, want_vals)
+        w = (C.c_uint32 * 13)(*[pow(2, 16 * j, M) for j in range(13)])
+        va = (C.c_uint32 * 8)(*(vals + [0] * (8 - len(vals))))
+        mu = (1 << 64) // M
+        d = vg.Pattern(pat, ci).device_dfa(F)
+        n_hit = 0
+        for dg in digests:
+            words = (C.c_uint32 * 8)(*[int.from_bytes(dg[4 * i:4 * i + 4], "little") if i < 5 else 0 for i in range(8)])
+            got = emu.emu_confirm_b58res(int(F), words, d["table"], d["accept"], d["sym_class"], d["n_classes"], d["start"], d["flags"],
+                                         M, len(vals), va, w, mu & 0xffffffff, mu >> 32)
+            want = oracle.regex_match(("(?i)" if ci else "") + pat, oracle.address_from_digest(fmt, dg))
+            assert got == int(want), (fmt, pat, dg.hex())
+            n_hit += want
+        assert n_hit > 0, (fmt, pat)
+    # patterns that are not a plain literal suffix get no residue test
+    for pat in ["[ab]c$", "a.c$", "abcdef$", "^1a$", "a|b$"]:
+        assert vg.Pattern(pat).lowering(F)["residue"] is None, pat
+
+
 def test_eth_literal_suffix_prefilter(emu):
     """Ethereum literal hex suffixes (F00$, 12$): the device compares the last digest bits with the lower-cased literal before
     the DFAs and the EIP-55 hash. The verdict must equal the oracle's regex over the checksummed address."""

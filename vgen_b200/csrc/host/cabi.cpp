@@ -282,6 +282,11 @@ int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, si
         snprintf(buf, sizeof buf, ";suffix=%08x:%08x", lp.dev.dfa.chk_mask, lp.dev.dfa.chk_value);
         s += buf;
     }
+    if (lp.dev.kind == VG_MATCH_DFA && lp.dev.dfa.b58_mod != 0) {      // Base58 literal suffix: payload mod 58^k in a small set
+        snprintf(buf, sizeof buf, ";residue=%x", lp.dev.dfa.b58_mod);
+        s += buf;
+        for (uint32_t i = 0; i < lp.dev.dfa.b58_nvals; i++) { snprintf(buf, sizeof buf, ":%x", lp.dev.dfa.b58_vals[i]); s += buf; }
+    }
     return copy_out(s, out, cap);
 }
 

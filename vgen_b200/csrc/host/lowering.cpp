@@ -306,6 +306,41 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             if (ok) { out.dev.dfa.chk_mask = (1u << (5 * (n - 1))) - 1u; out.dev.dfa.chk_value = value; }
         }
     }
+    if (format == VG_FMT_P2PKH || format == VG_FMT_P2PKH_UNCOMPRESSED || format == VG_FMT_P2SH_P2WPKH) {
+        // "Cat$": a literal of 1..5 Base58 characters anchored at the end = the payload modulo 58^k (up to 8 residues when
+        // the pattern is case-insensitive: every spelling the alphabet has)
+        const size_t n = pattern.size();
+        if (n >= 2 && n <= 6 && pattern[n - 1] == '$') {
+            std::vector<uint32_t> vals{0};
+            bool ok = true;
+            for (size_t i = 0; i + 1 < n && ok; i++) {
+                const char c = pattern[i];
+                std::string spell(1, c);
+                if (ci && c >= 'a' && c <= 'z') spell.push_back((char)(c - 32));
+                if (ci && c >= 'A' && c <= 'Z') spell.push_back((char)(c + 32));
+                std::vector<uint32_t> nx;
+                const bool alnum = (c >= '0' && c <= '9') || (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z');
+                for (char sc : spell) {
+                    const char *q = alnum ? strchr(B58_ALPHABET, sc) : nullptr;
+                    if (!q) continue;
+                    for (uint32_t v : vals) nx.push_back(v * 58u + (uint32_t)(q - B58_ALPHABET));
+                }
+                if (!alnum || nx.size() > 8) ok = false;        // a metacharacter, or too many spellings: no prefilter
+                vals.swap(nx);                                   // empty: no spelling is Base58 -> the DFA rejects every key anyway
+            }
+            if (ok && !vals.empty()) {
+                vg_dfa_dev &d = out.dev.dfa;
+                uint64_t M = 1;
+                for (size_t i = 0; i + 1 < n; i++) M *= 58;
+                d.b58_mod = (uint32_t)M; d.b58_nvals = (uint32_t)vals.size();
+                for (size_t i = 0; i < vals.size(); i++) d.b58_vals[i] = vals[i];
+                uint64_t w = 1 % M;
+                for (int j = 0; j < 13; j++) { d.b58_w[j] = (uint32_t)w; w = (w << 16) % M; }
+                const uint64_t mu = (uint64_t)((((unsigned __int128)1) << 64) / M);
+                d.b58_mu_lo = (uint32_t)mu; d.b58_mu_hi = (uint32_t)(mu >> 32);
+            }
+        }
+    }
     if (format == VG_FMT_ETHEREUM) {
         // "F00$", "dead$": a literal of 1..8 hex digits anchored at the end. Whatever the EIP-55 case turns out to be, the
         // lower-case hex of a matching address ends with the lower-cased literal: a test on the last digest bits.

@@ -13,8 +13,10 @@
 
 #ifdef VG_HOST_EMU
 #define VG_CLZ(x) ((uint32_t)__builtin_clz(x))
+static inline unsigned long long vg_umul64hi(unsigned long long a, unsigned long long b) { return (unsigned long long)(((unsigned __int128)a * b) >> 64); }
 #else
 #define VG_CLZ(x) ((uint32_t)__clz((int)(x)))
+__device__ __forceinline__ unsigned long long vg_umul64hi(unsigned long long a, unsigned long long b) { return __umul64hi(a, b); }
 #endif
 
 struct vg_dfa_view {
@@ -150,6 +152,23 @@ VG_DEV bool vg_match_base58check(const vg_matcher_dev &m, const vg_dfa_view &v, 
     uint32_t n[7];
     n[6] = (uint32_t)VERSION;
     n[5] = B[0]; n[4] = B[1]; n[3] = B[2]; n[2] = B[3]; n[1] = B[4]; n[0] = ck;
+    if (m.dfa.b58_mod != 0) {
+        // literal-suffix patterns (Cat$): the last k symbols are the payload mod 58^k. 13 multiply-adds over the 16-bit halves
+        // of the payload (each product < 2^46) and one Barrett reduction decide all but one key in 58^k before any division.
+        unsigned long long s = 0;
+        VG_UNROLL for (int j = 0; j < 13; j++) {
+            const uint32_t hw = (j == 12) ? n[6] : ((n[j >> 1] >> (16 * (j & 1))) & 0xffffu);
+            s += (unsigned long long)hw * m.dfa.b58_w[j];
+        }
+        const unsigned long long M = m.dfa.b58_mod, mu = ((unsigned long long)m.dfa.b58_mu_hi << 32) | m.dfa.b58_mu_lo;
+        const unsigned long long q = vg_umul64hi(s, mu);           // floor(s / M) - {0, 1, 2}
+        uint32_t r = (uint32_t)(s - q * M);                        // < 3 M < 2^32
+        if (r >= m.dfa.b58_mod) r -= m.dfa.b58_mod;
+        if (r >= m.dfa.b58_mod) r -= m.dfa.b58_mod;
+        bool any = false;
+        VG_UNROLL for (int k = 0; k < 8; k++) any = any || ((uint32_t)k < m.dfa.b58_nvals && r == m.dfa.b58_vals[k]);
+        if (!any) return false;
+    }
 #if VG_B58_TABLE
     if (v.b58) return vg_match_base58check_tab<VERSION>(m, v, n);
 #endif

@@ -31,6 +31,14 @@ struct vg_dfa_dev {
     // vg_match_segwit); chk_mask == 0: none. Ethereum, literal hex suffixes of at most 8 digits (F00$): the same pair over the last
     // 32 digest bits (big-endian), tested before the DFAs and the EIP-55 hash (vg_match_eth).
     uint32_t chk_mask, chk_value;
+    // Base58 formats, patterns that are a literal suffix of at most 5 characters (Cat$): the last k characters of the address are
+    // the 25-byte Base58Check payload mod 58^k, so (payload mod b58_mod) in b58_vals[0..b58_nvals) is a necessary condition that
+    // needs neither the 28 divisions of the radix conversion nor a DFA step (match.cuh vg_match_base58check); b58_mod == 0: none.
+    // b58_w[j] = 2^(16 j) mod b58_mod for the 13 half-words of the payload, b58_mu = floor(2^64 / b58_mod) (Barrett).
+    uint32_t b58_mod, b58_nvals;
+    uint32_t b58_vals[8];
+    uint32_t b58_w[13];
+    uint32_t b58_mu_lo, b58_mu_hi;
 };
 struct vg_matcher_dev {
     int kind;

@@ -40,7 +40,7 @@ class Pattern:
         return int(_cabi.lib().vgen_pattern_estimate_difficulty(int(fmt), self._pattern.encode(), int(self._ci)))
 
     def lowering(self, fmt):
-        """How the scan path will test this pattern on the device for `fmt`: dict(kind=..., intervals=[(lo, hi), ...], exact=..., suffix=(mask, value) or None, confirm="dfa" or None, residue=(58^k, value) or None)."""
+        """How the scan path will test this pattern on the device for `fmt`: dict(kind=..., intervals=[(lo, hi), ...], exact=..., suffix=(mask, value) or None, confirm="dfa" or None, residue=(58^k, value, ...) or None)."""
         buf = C.create_string_buffer(4096)
         rc = _cabi.lib().vgen_pattern_lowering(int(fmt), self._pattern.encode(), int(self._ci), buf, 4096)
         if rc < 0:
@@ -52,7 +52,7 @@ class Pattern:
                 out["exact"] = bytes.fromhex(p[6:])
             elif p.startswith("confirm="):      # "dfa": the device runs the DFA on the keys that pass the interval prefilter
                 out["confirm"] = p[8:]
-            elif p.startswith("residue="):      # (modulus 58^k, value): Base58 literal suffix, tested on the payload mod 58^k
+            elif p.startswith("residue="):      # (modulus 58^k, value, ...): Base58 literal suffix, tested on the payload mod 58^k
                 out["residue"] = tuple(int(x, 16) for x in p[8:].split(":"))
             elif p.startswith("suffix="):       # (mask, value) over the Bech32 checksum bits / the last 32 digest bits
                 out["suffix"] = tuple(int(x, 16) for x in p[7:].split(":"))
