@@ -40,6 +40,8 @@ def lib():
         L.vgo_base58check.argtypes = [C.c_char_p, C.c_int, C.c_char_p]
         L.vgo_base58_decode.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.vgo_segwit.argtypes = [C.c_int, C.c_char_p, C.c_int, C.c_char_p]
+        L.vgo_base58.argtypes = [C.c_char_p, C.c_int, C.c_char_p]
+        L.vgo_taproot_output.argtypes = [C.c_char_p, C.c_char_p]
         L.vgo_eip55.argtypes = [C.c_char_p, C.c_char_p]
         L.vgo_eip55.restype = None
         L.vgo_regex_check.argtypes = [C.c_char_p, C.c_int, C.c_char_p, C.c_int]
@@ -108,6 +110,20 @@ def keccak256(m):
 
 def base58check(m):
     o = C.create_string_buffer(256); lib().vgo_base58check(m, len(m), o); return o.value.decode()
+
+
+def base58(m):
+    o = C.create_string_buffer(2 * len(m) + 8); lib().vgo_base58(m, len(m), o); return o.value.decode()
+
+
+def base58_decode(s, cap=128):
+    o = C.create_string_buffer(cap); n = lib().vgo_base58_decode(s.encode(), o, cap); return None if n < 0 else o.raw[:n]
+
+
+def taproot_output(xonly):
+    """BIP341 key-path output key (no script tree) of an x-only internal key, or None if x is not on the curve."""
+    o = C.create_string_buffer(32)
+    return None if lib().vgo_taproot_output(bytes(xonly), o) else o.raw
 
 
 def segwit(witver, prog):

@@ -171,6 +171,24 @@ void vgo_keccak256(const uint8_t *m, uint64_t n, uint8_t *o) { keccak256(m, n, o
 int vgo_base58check(const uint8_t *m, int n, char *o) { return base58check_encode(m, n, o); }
 int vgo_base58_decode(const char *s, uint8_t *o, int cap) { return base58_decode(s, o, cap); }
 int vgo_segwit(int witver, const uint8_t *prog, int n, char *o) { return segwit_encode("bc", witver, prog, n, o); }
+int vgo_base58(const uint8_t *m, int n, char *o) { return base58_encode(m, n, o); }
+/* BIP341 key-path output key (no script tree) of an x-only INTERNAL key: lift_x (even y = (x^3 + 7)^((p+1)/4)), then the same
+ * tweak as format_digest(FMT_P2TR). For the published BIP341 / BIP86 vectors, which give internal public keys. -1: x not on the curve. */
+int vgo_taproot_output(const uint8_t xonly[32], uint8_t out[32]) {
+    static const uint64_t E[4] = {0xFFFFFFFFBFFFFF0CULL, ~0ULL, ~0ULL, 0x3FFFFFFFFFFFFFFFULL};   /* (p + 1) / 4 */
+    ge p; fe rhs, y, t, seven;
+    if (!g_table_ready) vgo_init();
+    fe_from_be(&p.x, xonly);
+    if (u256_cmp(p.x.d, FE_P) >= 0) return -1;
+    fe_sqr(&t, &p.x); fe_mul(&rhs, &t, &p.x); fe_set_u64(&seven, 7); fe_add(&rhs, &rhs, &seven);
+    fe_set_u64(&y, 1);
+    for (int i = 255; i >= 0; i--) { fe_sqr(&y, &y); if ((E[i >> 6] >> (i & 63)) & 1) fe_mul(&y, &y, &rhs); }
+    fe_sqr(&t, &y);
+    if (!fe_eq(&t, &rhs)) return -1;
+    if (fe_is_odd(&y)) fe_neg(&y, &y);
+    p.y = y; p.inf = 0;
+    return format_digest(FMT_P2TR, &p, out) == 32 ? 0 : -1;
+}
 void vgo_eip55(const uint8_t *a, char *o) { eip55_encode(a, o); }
 int vgo_fe_selftest(void) {
     fe a, b, c, one; fe_from_be(&a, GX_BE); fe_inv(&b, &a); fe_mul(&c, &a, &b); fe_set_u64(&one, 1);

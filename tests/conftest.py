@@ -25,3 +25,11 @@ def regex_golden():
     import json
     with open(os.path.join(ROOT, "tests", "golden", "regex_cases.json")) as f:
         return json.load(f)
+
+
+@pytest.fixture(scope="session")
+def published():
+    """Vectors copied from published specifications (tests/golden/published.json; sources cited inside)."""
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "published.json")) as f:
+        return json.load(f)

@@ -142,12 +142,15 @@ def test_scan_match_sets_small(small_runner, case):
     assert len(res.matches) > 0, "vacuous case: resize it"
 
 
-@pytest.mark.parametrize("fmt,pat", [("p2tr", "^bc1q"), ("p2pkh", "^3"), ("p2sh-p2wpkh", "^(3Ab|3Cd)$"), ("p2wpkh", "^1"), ("ethereum", "^0xg")])
-def test_scan_patterns_that_cannot_match(small_runner, fmt, pat):
-    """Patterns no address of the format can match: the lowering says so ("none") and the scan reports the range as scanned."""
+@pytest.mark.parametrize("fmt,pat,kind", [("p2tr", "^bc1q", "none"), ("p2pkh", "^3", "none"), ("p2wpkh", "^1", "none"), ("ethereum", "^0xg", "none"),
+                                          ("p2sh-p2wpkh", "^(3Ab|3Cd)$", "intervals")])
+def test_scan_patterns_that_cannot_match(small_runner, fmt, pat, kind):
+    """Patterns no address of the format can match. Where the lowering can tell (a prefix outside the format's head or alphabet) it
+    says "none" and the scan reports the range as scanned without a launch; where it cannot (a 3-character exact string: every
+    address is longer) the interval prefilter + device DFA find nothing. Either way: no matches, every key counted."""
     res = _check_scan(small_runner, fmt, pat, 2**64, 1 << 16)
     assert res.matches == [] and res.operations == 1 << 16
-    assert small_runner.matcher_kind() == "none"
+    assert small_runner.matcher_kind() == kind
 
 
 def test_scan_edges(small_runner):
@@ -183,6 +186,31 @@ def test_scan_exact_address_planted(runner):
     assert [int(m.hex, 16) for m in res.matches] == [start + off]
     assert res.matches[0].address == addr and res.operations == n
     assert runner.matcher_kind() == "exact"
+
+
+def test_p2tr_published_bip341_vector(small_runner, published):
+    """BIP341 wallet-test-vectors: internalPrivkey -> output key -> bc1p address, through both GPU stages (walk + TapTweak)."""
+    v = published["taproot"]["vectors"][0]
+    k = int(v["internal_privkey"], 16)
+    assert small_runner.digest_batch("p2tr", k, 1).hex() == v["output_key"]
+    res = _scan(small_runner, "p2tr", "^" + v["address"] + "$", k - 1000, 3000)
+    assert [(int(m.hex, 16), m.address) for m in res.matches] == [(k, v["address"])]
+    small_runner.dispatch_p2tr(k, 0, n=8)
+    assert small_runner.await_result_p2tr(0)[0][0].hex() == v["internal_pubkey"]
+
+
+def test_published_key_to_address_vectors(small_runner, published):
+    """Bitcoin wiki worked example (private key -> compressed public key -> P2PKH address) and the WIF example, on the GPU path."""
+    v = published["base58check_p2pkh"]["vectors"][1]
+    k = int(v["key"], 16)
+    assert small_runner.generate_batch(k, 1)[0].hex() == v["hash160"]
+    res = _scan(small_runner, "p2pkh", "^" + v["address"] + "$", k - 5, 10)
+    assert [(m.address, int(m.hex, 16)) for m in res.matches] == [(v["address"], k)]
+    w = published["wif"]["vectors"][0]
+    res = _scan(small_runner, "p2pkh-uncompressed", ".", int(w["key"], 16), 1)
+    assert res.matches[0].wif == w["wif_uncompressed"] and res.matches[0].address == "1GAehh7TsJAHuUAeKZcXf5CnwuGuGgyX2S"
+    res = _scan(small_runner, "p2pkh", ".", int(w["key"], 16), 1)
+    assert res.matches[0].wif == w["wif_compressed"]
 
 
 def test_p2tr_exact_address_planted(small_runner):

@@ -281,3 +281,39 @@ def test_literal_suffix_lowering():
         assert vg.Pattern(pat).lowering(F.Ethereum)["suffix"] is None, pat
     for fmt in (F.P2pkh, F.P2shP2wpkh, F.P2pkhUncompressed):
         assert vg.Pattern("dead$").lowering(fmt)["suffix"] is None
+
+
+def test_published_vectors_through_the_product_encoders(published):
+    """The product's own host encoders (vgen_format_address / vgen_format_wif / vgen_parse_key, host_util.cpp — what turns a device
+    hit into the reported strings) against vectors copied from the specifications (tests/golden/published.json)."""
+    F = vg.AddressFormat
+    for a in published["eip55"]["addresses"]:                                     # EIP-55 (Keccak-256 inside)
+        assert vg.address_from_digest(F.Ethereum, bytes.fromhex(a[2:])) == a
+    for v in published["base58check_p2pkh"]["vectors"]:                           # Base58Check (double SHA-256 inside)
+        assert vg.address_from_digest(F.P2pkh, bytes.fromhex(v["hash160"])) == v["address"]
+        assert vg.address_from_digest(F.P2pkhUncompressed, bytes.fromhex(v["hash160"])) == v["address"]
+    for v in published["segwit"]["vectors"]:                                      # BIP173 / BIP350
+        prog = bytes.fromhex(v["program"])
+        if v["witver"] == 0 and len(prog) == 20:
+            assert vg.address_from_digest(F.P2wpkh, prog) == v["address"].lower()
+        if v["witver"] == 1 and len(prog) == 32:
+            assert vg.address_from_digest(F.P2tr, prog) == v["address"].lower()
+    for v in published["taproot"]["vectors"]:                                     # BIP341 / BIP86 output key -> address
+        assert vg.address_from_digest(F.P2tr, bytes.fromhex(v["output_key"])) == v["address"]
+    for v in published["wif"]["vectors"]:
+        k = bytes.fromhex(v["key"])
+        assert vg.wif_from_key(F.P2pkhUncompressed, k) == v["wif_uncompressed"]
+        assert vg.wif_from_key(F.P2pkh, k) == v["wif_compressed"] == vg.wif_from_key(F.P2wpkh, k)
+        from vgen_b200 import _cabi
+        for wif, comp in ((v["wif_uncompressed"], 0), (v["wif_compressed"], 1)):
+            out, is_wif, compressed = C.create_string_buffer(32), C.c_int(-1), C.c_int(-1)
+            assert _cabi.lib().vgen_parse_key(wif.encode(), out, C.byref(is_wif), C.byref(compressed)) == 0
+            assert (out.raw, is_wif.value, compressed.value) == (k, 1, comp)
+    # exact-address patterns are decoded on the host (Base58Check / Bech32(m) decode + checksum): published address -> digest
+    v = published["base58check_p2pkh"]["vectors"][1]
+    assert vg.Pattern("^" + v["address"] + "$").lowering(F.P2pkh)["exact"].hex() == v["hash160"]
+    t = published["taproot"]["vectors"][0]
+    assert vg.Pattern("^" + t["address"] + "$").lowering(F.P2tr)["exact"].hex() == t["output_key"]
+    e = published["eip55"]["addresses"][4]
+    assert vg.Pattern("^" + e + "$").lowering(F.Ethereum)["exact"].hex() == e[2:].lower()
+    assert vg.Pattern("^" + e.lower() + "$").lowering(F.Ethereum)["kind"] == "none"      # wrong case can never match the EIP-55 form
