@@ -129,6 +129,10 @@ SMALL_CASES = [
     ("p2wpkh", "qq$", False), ("p2wpkh", "ZQ$", True), ("p2tr", "7$", False), ("ethereum", "1f$", False), ("ethereum", "AB$", True),
     ("ethereum", "AB$", False), ("ethereum", "07$", False),
     ("p2pkh", "at$", False), ("p2pkh", "AT$", True), ("p2sh-p2wpkh", "Zz$", False), ("p2pkh-uncompressed", "7$", False),
+    # the wider regex surface (round 2): word boundaries, flag x, nested classes / set operators, \\p{..}, and a pattern whose DFA
+    # is too large for a device table (the device reports every key, the host decides with the NFA)
+    ("p2pkh", r"at\b", False), ("p2pkh", r"^\b1C\B", False), ("p2wpkh", "(?x) q q $ # two q", False), ("p2pkh", "[a-z&&[^aeiou]]{4}$", False),
+    ("ethereum", r"\p{Lu}{4}$", False), ("p2sh-p2wpkh", "[A-Z--[A-M]]{3}", False), ("p2pkh", "a.{13}$", False, 1 << 14),
     # a prefix and a tail: interval prefilter + device DFA on the survivors (vg_matcher_dev::confirm_dfa)
     ("p2pkh", "^1C.*z$", False), ("p2wpkh", "^bc1qa.*zz$", False), ("ethereum", "^0xAb", False), ("p2sh-p2wpkh", "^3A.*[0-9]$", False),
 ]

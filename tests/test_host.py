@@ -317,3 +317,29 @@ def test_published_vectors_through_the_product_encoders(published):
     e = published["eip55"]["addresses"][4]
     assert vg.Pattern("^" + e + "$").lowering(F.Ethereum)["exact"].hex() == e[2:].lower()
     assert vg.Pattern("^" + e.lower() + "$").lowering(F.Ethereum)["kind"] == "none"      # wrong case can never match the EIP-55 form
+
+
+def test_regex_too_big_for_a_device_table_falls_back_to_the_host_nfa(regex_golden):
+    """A pattern vgen accepts must not become an error after the swap (src/pattern.rs:21-40 takes whatever `regex` compiles).
+    `a.{13}$` needs 2^14 DFA states, more than a device table holds: Pattern still compiles, matches() decides with the NFA, and
+    the lowering says the device will report a superset (every key, or the prefix intervals) for the host to confirm."""
+    F = vg.AddressFormat
+    for pat in ("a.{13}$", "^1C.*a.{13}$", "(a|b).{12}[0-9]$"):
+        p = vg.Pattern(pat)
+        for h in regex_golden["haystacks"]:
+            assert p.matches(h) == bool(re.search(pat, h)), (pat, h)
+    low = vg.Pattern("a.{13}$").lowering(F.P2pkh)
+    assert low["kind"] == "all" and low["confirm"] == "host-nfa", low
+    low = vg.Pattern("^1Ca.*a.{13}$").lowering(F.P2pkh)
+    assert low["kind"] == "intervals" and low["confirm"] == "host-nfa" and len(low["intervals"]) == 2, low
+    assert vg.Pattern("a.{5}$").lowering(F.P2pkh)["confirm"] is None          # small enough: a device DFA as before
+
+
+def test_word_boundary_is_one_bit_of_look_behind_in_the_dfa():
+    """\\b / \\B compile into the dense DFA (state = NFA set x "previous byte was a word byte"), so they run on the device too."""
+    F = vg.AddressFormat
+    d = vg.Pattern(r"\bCat\b").device_dfa(F.P2pkh)
+    assert 0 < d["n_states"] < 64
+    for pat, text, want in [(r"\bcat\b", "a cat b", True), (r"\bcat\b", "acat", False), (r"\bcat\b", "cat", True), (r"cat\B", "cats", True),
+                            (r"cat\B", "cat", False), (r"\B", "", True), (r"\b", "", False), (r"\b", "a", True), (r"^\B", "-", True)]:
+        assert vg.Pattern(pat).matches(text) is want, (pat, text)

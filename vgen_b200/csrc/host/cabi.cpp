@@ -12,6 +12,8 @@ struct vgen_ctx {
     vg::Engine engine;
     std::string last_error;
     std::vector<vg::Hit> hits;     // confirmed hits of the last scan, ascending by key
+    std::string text;              // their text records (vg::Hit::text_off / text_len), in hit order
+    bool all_text = false;         // every hit has a text record: the records of any hit range are one contiguous piece of `text`
 };
 static void export_hit(const vg::Hit &h, vgen_hit &o) {
     h.key.to_be(o.key_be);
@@ -97,7 +99,9 @@ int vgen_cuda_scan(vgen_ctx *ctx, const uint8_t start_be[32], const uint8_t *end
         hits.clear();
         vg::Engine::Progress cb;
         if (progress) cb = [&](uint64_t k) { progress(k, user); };
-        if (!ctx->engine.scan(start, end_be ? &end : nullptr, max_hits, stop, cb, hits, *keys_scanned, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+        if (!ctx->engine.scan(start, end_be ? &end : nullptr, max_hits, stop, cb, hits, ctx->text, *keys_scanned, err)) return fail(ctx, VGEN_ERR_CUDA, err);
+        ctx->all_text = true;
+        for (const vg::Hit &h : hits) if (h.text_len == 0) { ctx->all_text = false; break; }
         uint64_t n = std::min<uint64_t>(hits.size(), hits_cap);
         for (uint64_t i = 0; i < n; i++) export_hit(hits[i], hits_out[i]);
         *n_hits = n;
@@ -136,12 +140,25 @@ int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t
     if (cap < 1) return VGEN_ERR_BUFFER;
     n = std::min<uint64_t>(n, (cap - 1) / kRec);
     if (n == 0) return VGEN_ERR_BUFFER;
+    if (ctx->all_text) {
+        // the scan's confirm jobs built every record: the records of hits [offset, offset + n) are one piece of the text blob
+        const vg::Hit *H = ctx->hits.data() + offset;
+        const uint64_t t0 = H[0].text_off;
+        uint64_t lo = 0, hi = n;                                   // largest count whose bytes fit in cap - 1
+        while (lo < hi) { uint64_t mid = (lo + hi + 1) / 2; if (H[mid - 1].text_off + H[mid - 1].text_len - t0 <= cap - 1) lo = mid; else hi = mid - 1; }
+        if (lo == 0) return VGEN_ERR_BUFFER;
+        const size_t bytes = (size_t)(H[lo - 1].text_off + H[lo - 1].text_len - t0);
+        memcpy(buf, ctx->text.data() + t0, bytes);
+        buf[bytes] = 0;
+        *n_written = lo;
+        return (int64_t)bytes;
+    }
     std::vector<std::string> lines(n);
     unsigned nt = std::max(1u, std::min<unsigned>(std::thread::hardware_concurrency(), (unsigned)(n / 256 + 1)));
     auto work = [&](unsigned t) {
         for (uint64_t i = t; i < n; i += nt) {
             const vg::Hit &h = ctx->hits[offset + i];
-            if (!h.text.empty()) continue;                        // already built by the scan's confirm job
+            if (h.text_len) { lines[i].assign(ctx->text, (size_t)h.text_off, h.text_len); continue; }      // built by the scan's confirm job
             uint8_t kb[32]; h.key.to_be(kb);
             lines[i] = vg::h_hex(kb, 32) + " " + vg::format_address(fmt, h.digest) + " " + vg::format_wif(fmt, kb) + "\n";
         }
@@ -151,10 +168,7 @@ int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t
     work(0);
     for (auto &x : th) x.join();
     size_t pos = 0;
-    for (uint64_t i = 0; i < n; i++) {
-        const std::string &l = lines[i].empty() ? ctx->hits[offset + i].text : lines[i];
-        memcpy(buf + pos, l.data(), l.size()); pos += l.size();
-    }
+    for (uint64_t i = 0; i < n; i++) { memcpy(buf + pos, lines[i].data(), lines[i].size()); pos += lines[i].size(); }
     buf[pos] = 0;
     *n_written = n;
     return (int64_t)pos;
@@ -277,6 +291,7 @@ int vgen_pattern_lowering(int format, const char *pattern, int ci, char *out, si
         s += ";exact=";
         for (int i = 0; i < lp.dev.exact_words * 4; i++) { snprintf(buf, sizeof buf, "%02x", (lp.dev.exact[i / 4] >> (8 * (i % 4))) & 0xff); s += buf; }
     }
+    if (lp.host_regex) s += ";confirm=host-nfa";      // DFA too large for the device: superset on the device, exact NFA match on the host
     if (lp.dev.confirm_dfa) s += ";confirm=dfa";       // the device runs the DFA on the keys that pass the prefilter
     if (lp.dev.kind == VG_MATCH_DFA && lp.dev.dfa.chk_mask != 0) {      // literal-suffix test ahead of the DFA (scan_types.h)
         snprintf(buf, sizeof buf, ";suffix=%08x:%08x", lp.dev.dfa.chk_mask, lp.dev.dfa.chk_value);

@@ -41,7 +41,7 @@ WorkerPool::~WorkerPool() {
 }
 void WorkerPool::run() {
     for (;;) {
-        std::packaged_task<std::vector<Hit>()> job;
+        std::packaged_task<HitBatch()> job;
         {
             std::unique_lock<std::mutex> lk(mu_);
             cv_.wait(lk, [this] { return stop_ || !q_.empty(); });
@@ -51,9 +51,9 @@ void WorkerPool::run() {
         job();
     }
 }
-std::future<std::vector<Hit>> WorkerPool::submit(std::function<std::vector<Hit>()> fn) {
-    std::packaged_task<std::vector<Hit>()> task(std::move(fn));
-    std::future<std::vector<Hit>> f = task.get_future();
+std::future<HitBatch> WorkerPool::submit(std::function<HitBatch()> fn) {
+    std::packaged_task<HitBatch()> task(std::move(fn));
+    std::future<HitBatch> f = task.get_future();
     { std::lock_guard<std::mutex> g(mu_); q_.push_back(std::move(task)); }
     cv_.notify_one();
     return f;
@@ -199,20 +199,21 @@ bool Engine::set_shard(uint32_t index, uint32_t count, std::string &err) {
 
 bool Engine::upload_dfa(std::string &err) {
     const Dfa &d = lp_.dfa;
+    // the kernel stages both arrays word-wise: whole words, tail cleared
+    const size_t tb = (d.table.size() * 2 + 7) & ~(size_t)3, ab = (d.accept_end.size() + 7) & ~(size_t)3;
+    std::vector<uint8_t> tbuf(tb, 0), abuf(ab, 0);
+    memcpy(tbuf.data(), d.table.data(), d.table.size() * 2);
+    memcpy(abuf.data(), d.accept_end.data(), d.accept_end.size());
     for (auto &D : devices_) {
         if (D.failed) continue;
         CK(cudaSetDevice(D.device));
-        if (D.d_dfa_table) { cudaFree(D.d_dfa_table); D.d_dfa_table = nullptr; }
-        if (D.d_dfa_accept) { cudaFree(D.d_dfa_accept); D.d_dfa_accept = nullptr; }
-        // the kernel stages both arrays word-wise: round the allocations up to whole words and clear the tail
-        const size_t tb = (d.table.size() * 2 + 7) & ~(size_t)3, ab = (d.accept_end.size() + 7) & ~(size_t)3;
-        CK(cudaMalloc(&D.d_dfa_table, tb));
-        CK(cudaMalloc(&D.d_dfa_accept, ab));
-        CK(cudaMemset(D.d_dfa_table, 0, tb));
-        CK(cudaMemset(D.d_dfa_accept, 0, ab));
-        CK(cudaMemcpy(D.d_dfa_table, d.table.data(), d.table.size() * 2, cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(D.d_dfa_accept, d.accept_end.data(), d.accept_end.size(), cudaMemcpyHostToDevice));
+        // buffers are kept and reused when the new tables fit: cudaFree / cudaMalloc synchronise the device
+        if (D.dfa_table_cap < tb) { if (D.d_dfa_table) cudaFree(D.d_dfa_table); D.d_dfa_table = nullptr; CK(cudaMalloc(&D.d_dfa_table, std::max<size_t>(tb, 4096))); D.dfa_table_cap = std::max<size_t>(tb, 4096); }
+        if (D.dfa_accept_cap < ab) { if (D.d_dfa_accept) cudaFree(D.d_dfa_accept); D.d_dfa_accept = nullptr; CK(cudaMalloc(&D.d_dfa_accept, std::max<size_t>(ab, 1024))); D.dfa_accept_cap = std::max<size_t>(ab, 1024); }
+        CK(cudaMemcpy(D.d_dfa_table, tbuf.data(), tb, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(D.d_dfa_accept, abuf.data(), ab, cudaMemcpyHostToDevice));
     }
+    dfa_uploaded_ = true;
     return true;
 }
 
@@ -270,6 +271,9 @@ bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
 }
 
 bool Engine::set_pattern(int format, const std::string &pattern, bool ci, std::string &err) {
+    // the same pattern again (scan after scan through scan_gpu_with_runner): nothing to lower, nothing to upload
+    if (has_pattern_ && dfa_uploaded_ && lp_.format == format && lp_.pattern == pattern && lp_.case_insensitive == ci) return true;
+    dfa_uploaded_ = false;
     LoweredPattern lp;
     if (!lower_pattern(format, pattern, ci, lp, err)) return false;
     lp_ = lp;
@@ -357,7 +361,7 @@ bool Engine::launch_window(Lane &L, Slot &S, int fmt, int mode, uint8_t *dump, u
 
 // ---- one scan ----
 namespace {
-struct WindowResult { uint64_t keys = 0; std::vector<std::future<std::vector<Hit>>> jobs; };
+struct WindowResult { uint64_t keys = 0; std::vector<std::future<HitBatch>> jobs; };
 }
 // hit records of one collected window (or of one piece of a window that overflowed its hit buffer), already split by key
 // index into the buckets the confirm jobs take
@@ -568,10 +572,11 @@ void Engine::device_worker(ScanRun &R, int di) {
             wr.jobs.push_back(pool_->submit([this, recs, base, dev_index, fmt, with_text]() {
                 // records in key order (the device appends them in atomic order)
                 std::sort(recs->begin(), recs->end(), [](const vg_hit_rec &a, const vg_hit_rec &b) { return a.idx_hi != b.idx_hi ? a.idx_hi < b.idx_hi : a.idx_lo < b.idx_lo; });
-                std::vector<Hit> out;
-                out.reserve(recs->size());
+                HitBatch out;
+                out.hits.reserve(recs->size());
+                if (with_text) out.text.reserve(recs->size() * 160);
                 for (const vg_hit_rec &rec : *recs) {
-                    Hit h; memset(h.digest, 0, 32);
+                    Hit h; memset(&h, 0, sizeof h);
                     h.digest_len = (uint32_t)digest_len_of_format(fmt); h.lane = dev_index;
                     for (int w = 0; w < 8; w++) for (int b = 0; b < 4; b++) h.digest[4 * w + b] = (uint8_t)(rec.digest[w] >> (8 * b));
                     // exact confirmation on the host: re-encode the address from the digest and run the full DFA
@@ -580,9 +585,11 @@ void Engine::device_worker(ScanRun &R, int di) {
                     h.key = base.add64(((uint64_t)rec.idx_hi << 32) | rec.idx_lo);
                     if (with_text) {
                         uint8_t kb[32]; h.key.to_be(kb);
-                        h.text = h_hex(kb, 32) + " " + addr + " " + format_wif(fmt, kb) + "\n";
+                        h.text_off = out.text.size();
+                        out.text += h_hex(kb, 32); out.text += ' '; out.text += addr; out.text += ' '; out.text += format_wif(fmt, kb); out.text += '\n';
+                        h.text_len = (uint32_t)(out.text.size() - h.text_off);
                     }
-                    out.push_back(std::move(h));
+                    out.hits.push_back(h);
                 }
                 return out;
             }));
@@ -599,8 +606,8 @@ void Engine::device_worker(ScanRun &R, int di) {
 }
 
 bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, const volatile int32_t *stop, const Progress &progress,
-                  std::vector<Hit> &hits, uint64_t &keys_scanned, std::string &err) {
-    hits.clear(); keys_scanned = 0;
+                  std::vector<Hit> &hits, std::string &text, uint64_t &keys_scanned, std::string &err) {
+    hits.clear(); text.clear(); keys_scanned = 0;
     if (!has_pattern_) { err = "no pattern set"; return false; }
     // valid scalars are 1..n-1 (src/address.rs:93); scalars outside are skipped, not counted (src/scanner.rs:294-295)
     U256 start = start_in, end = end_in ? *end_in : secp_order_minus1();
@@ -665,8 +672,13 @@ bool Engine::scan(const U256 &start_in, const U256 *end_in, uint64_t max_hits, c
             lk.unlock();
             R.cv_work.notify_all();
             for (auto &f : wr.jobs) {
-                std::vector<Hit> v = f.get();
-                if (!stopping) for (auto &h : v) hits.push_back(std::move(h));
+                HitBatch v = f.get();
+                if (stopping || v.hits.empty()) continue;
+                const uint64_t shift = text.size();
+                const size_t at = hits.size();
+                hits.insert(hits.end(), v.hits.begin(), v.hits.end());
+                if (shift) for (size_t i = at; i < hits.size(); i++) hits[i].text_off += shift;
+                text += v.text;
             }
             if (!stopping) {
                 keys_scanned += wr.keys;

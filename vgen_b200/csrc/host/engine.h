@@ -21,8 +21,12 @@
 
 namespace vg {
 
-// text: "<key hex> <address> <wif>\n", filled by the per-window confirm job when the window is sparse (else empty: formatted on demand)
-struct Hit { U256 key; uint8_t digest[32]; uint32_t digest_len; uint32_t lane; std::string text; };
+// A confirmed hit. Its text record "<key hex> <address> <wif>\n" is built by the per-window confirm job when the window is sparse
+// and lives in the scan's text blob at [text_off, text_off + text_len) (text_len == 0: formatted on demand). Plain data, so that
+// merging a window is two bulk appends (records, text) whatever the number of hits.
+struct Hit { U256 key; uint8_t digest[32]; uint32_t digest_len; uint32_t lane; uint64_t text_off; uint32_t text_len; };
+// what one confirm job hands back: hits in ascending key order, text offsets relative to `text`
+struct HitBatch { std::vector<Hit> hits; std::string text; };
 
 // One window of the fixed window sequence of a scan (plan.h). `seq` orders the windows of this context by key, `logical` is
 // the plan lane the window belongs to (normally run by the physical lane of the same index; by any surviving lane once its
@@ -61,6 +65,7 @@ struct Device {
     std::string name;
     uint32_t *d_pow2 = nullptr, *d_gtab = nullptr, *d_tap_table = nullptr;
     uint16_t *d_dfa_table = nullptr; uint8_t *d_dfa_accept = nullptr;
+    size_t dfa_table_cap = 0, dfa_accept_cap = 0;   // bytes allocated (buffers are reused by later patterns that fit)
     std::vector<int> lanes;                      // indices into Engine::lanes_
     bool failed = false;                         // a CUDA call failed on it (or a fault was injected): its windows go to the other devices
     std::string failure;
@@ -71,13 +76,13 @@ class WorkerPool {
 public:
     explicit WorkerPool(unsigned n);
     ~WorkerPool();
-    std::future<std::vector<Hit>> submit(std::function<std::vector<Hit>()> fn);
+    std::future<HitBatch> submit(std::function<HitBatch()> fn);
     unsigned size() const { return (unsigned)threads_.size(); }
 private:
     void run();
     std::mutex mu_;
     std::condition_variable cv_;
-    std::deque<std::packaged_task<std::vector<Hit>()>> q_;
+    std::deque<std::packaged_task<HitBatch()>> q_;
     std::vector<std::thread> threads_;
     bool stop_ = false;
 };
@@ -92,8 +97,9 @@ public:
     bool set_stream(int lane, cudaStream_t s, std::string &err);
     typedef std::function<void(uint64_t)> Progress;
     // scans [start, end] (end == nullptr: to n-1); hits sorted ascending, truncated to max_hits (0 = unlimited)
+    // `text`: the text records of the hits that have one (Hit::text_off / text_len), in hit order
     bool scan(const U256 &start, const U256 *end, uint64_t max_hits, const volatile int32_t *stop, const Progress &progress,
-              std::vector<Hit> &hits, uint64_t &keys_scanned, std::string &err);
+              std::vector<Hit> &hits, std::string &text, uint64_t &keys_scanned, std::string &err);
     // digests of n sequential keys from start (stride bytes each, zero-filled for invalid scalars)
     bool digest_batch(int format, const U256 &start, uint64_t n, uint8_t *out, uint32_t stride, std::string &err);
     // device-resident timing of n_windows full-size windows per device, all devices of the context at once (bench `value`
@@ -141,6 +147,7 @@ private:
     uint32_t stride_lanes_ = 0;    // lane count the stride points were computed for
     LoweredPattern lp_;
     bool has_pattern_ = false;
+    bool dfa_uploaded_ = false;    // the devices hold lp_'s DFA
     bool p2tr_internal_ = false;   // digest_batch only: dump the untweaked internal keys instead of running the tweak stage
     std::unique_ptr<WorkerPool> pool_;
 };

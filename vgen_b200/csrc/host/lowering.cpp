@@ -263,7 +263,7 @@ static bool intervals_from_prefixes(int format, const std::vector<std::string> &
     // a-f from A-F (Ethereum ^0xAb: the intervals ignore the EIP-55 case): the device then runs the staged DFA on the
     // survivors, so that only real matches cross PCIe. Without it every prefix candidate (1.3 M records per 77.6 M-key window
     // for a 2-character Base58 prefix) would be re-encoded on the host and the scan would be host-bound.
-    if (!decides || (format == VG_FMT_ETHEREUM && (out.dev.dfa.flags & 1u))) out.dev.confirm_dfa = 1;
+    if (!out.host_regex && (!decides || (format == VG_FMT_ETHEREUM && (out.dev.dfa.flags & 1u)))) out.dev.confirm_dfa = 1;
     return true;
 }
 
@@ -274,7 +274,10 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
     if (!compile_pattern(pattern, ci, out.dfa, out.info, err)) { err = "Invalid regex pattern: " + pattern + ": " + err; return false; }   // src/pattern.rs:32-33
     memset(&out.dev, 0, sizeof out.dev);
     fill_device_dfa(format, out.dfa, out.dev.dfa);
-    if (format == VG_FMT_ETHEREUM && (out.dev.dfa.flags & 1u)) {
+    // A pattern whose DFA is too large for a device table (regex_dfa.cpp): the device reports a superset - every key, or the keys
+    // inside the intervals of a literal prefix when the pattern has one - and the host decides with the NFA. Exact, host-bound.
+    out.host_regex = !out.dfa.table_complete;
+    if (format == VG_FMT_ETHEREUM && (out.dev.dfa.flags & 1u) && !out.host_regex) {
         // the pattern tells a-f from A-F, so the device needs the EIP-55 checksum hash of a key before it can run the DFA.
         // Append the same pattern compiled case-insensitively: it accepts the lower-case hex of every address the pattern
         // matches, needs no hash, and rejects almost every key (measured: F00$ 1,785 -> see profiles/configs_r01_c.log).
@@ -291,6 +294,11 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             d.table_u16 = (uint32_t)out.dfa.table.size(); d.accept_bytes = (uint32_t)out.dfa.accept_end.size();
         }
     }
+    if (out.host_regex) {
+        out.dev.kind = VG_MATCH_ALL; out.kind_name = "all";
+        const PatternInfo &hi = out.info;
+        if (!hi.anchored_start || hi.prefix_sets.empty()) return true;
+    } else
     if (format == VG_FMT_P2WPKH || format == VG_FMT_P2TR) {
         // "dead$": a literal of 1..6 Bech32 characters anchored at the end lies inside the checksum symbols
         static const char *charset = "qpzry9x8gf2tvdw0s3jn54khce6mua7l";
@@ -306,7 +314,7 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             if (ok) { out.dev.dfa.chk_mask = (1u << (5 * (n - 1))) - 1u; out.dev.dfa.chk_value = value; }
         }
     }
-    if (format == VG_FMT_P2PKH || format == VG_FMT_P2PKH_UNCOMPRESSED || format == VG_FMT_P2SH_P2WPKH) {
+    if (!out.host_regex && (format == VG_FMT_P2PKH || format == VG_FMT_P2PKH_UNCOMPRESSED || format == VG_FMT_P2SH_P2WPKH)) {
         // "Cat$": a literal of 1..5 Base58 characters anchored at the end = the payload modulo 58^k (up to 8 residues when
         // the pattern is case-insensitive: every spelling the alphabet has)
         const size_t n = pattern.size();
@@ -341,7 +349,7 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             }
         }
     }
-    if (format == VG_FMT_ETHEREUM) {
+    if (!out.host_regex && format == VG_FMT_ETHEREUM) {
         // "F00$", "dead$": a literal of 1..8 hex digits anchored at the end. Whatever the EIP-55 case turns out to be, the
         // lower-case hex of a matching address ends with the lower-cased literal: a test on the last digest bits.
         const size_t n = pattern.size();
@@ -356,8 +364,7 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
             if (ok) { out.dev.dfa.chk_mask = n - 1 == 8 ? 0xffffffffu : (1u << (4 * (n - 1))) - 1u; out.dev.dfa.chk_value = value; }
         }
     }
-    out.dev.kind = VG_MATCH_DFA;
-    out.kind_name = "dfa";
+    if (!out.host_regex) { out.dev.kind = VG_MATCH_DFA; out.kind_name = "dfa"; }
     const PatternInfo &info = out.info;
     if (!info.anchored_start || info.prefix_sets.empty()) return true;
 
@@ -389,7 +396,7 @@ static bool lower_syntactic(int format, const std::string &pattern, bool ci, Low
 
 bool lower_pattern(int format, const std::string &pattern, bool ci, LoweredPattern &out, std::string &err) {
     if (!lower_syntactic(format, pattern, ci, out, err)) return false;
-    if (out.dev.kind != VG_MATCH_DFA || !out.info.anchored_start) return true;
+    if (out.dev.kind != VG_MATCH_DFA || !out.info.anchored_start || out.host_regex) return true;
     // anchored, but the leading run of character sets decided nothing (alternations such as ^(1Cat|1Dog), ^bc1q(aa|zz),
     // optional groups): take the prefixes from the DFA. Superset semantics: the host confirmation decides.
     std::vector<std::string> pf; bool complete = false;

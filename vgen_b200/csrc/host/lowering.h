@@ -15,6 +15,7 @@ struct LoweredPattern {
     vg_matcher_dev dev;      // device matcher (DFA table pointers are filled by the engine per device)
     double density = 1.0;    // upper estimate of the fraction of keys the DEVICE matcher reports (1 = unknown / may be dense)
     std::string kind_name;   // "intervals" | "exact" | "dfa" | "all" | "none"
+    bool host_regex = false; // the DFA is too large for the device: it reports a superset (all keys / prefix intervals), the host decides with the NFA
 };
 // shared-memory bytes the walk kernel needs to stage this DFA (table + accept + symbol classes), 0 if it is too large
 uint32_t dfa_smem_bytes(const vg_dfa_dev &d);

@@ -211,18 +211,43 @@ class GpuRunner:
         return out, scanned.value
 
     def fetch_text(self, total):
-        """bytes: "<key hex> <address> <wif>\\n" for every hit of the last scan (vgen_cuda_scan_fetch_text), copied out of the library."""
-        chunks, got = [], 0
-        cap = 1 << 22
+        """"<key hex> <address> <wif>\\n" for every hit of the last scan (vgen_cuda_scan_fetch_text), copied out of the library into
+        ONE caller-owned buffer. Returns (bytes-like, hits)."""
+        if total <= 0:
+            return b"", 0
+        cap = min(total * 227 + 1, 1 << 28)               # 227 = the library's bound for one record
+        store = bytearray(cap)
+        buf = (C.c_char * cap).from_buffer(store)
+        n = C.c_uint64(0)
+        got = pos = 0
+        while got < total:
+            room = C.cast(C.byref(buf, pos), C.c_void_p)
+            nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, got, total - got, room, cap - pos, C.byref(n)))
+            if nb <= 0 or n.value == 0:
+                if pos == 0 or cap - pos >= 228:
+                    break
+                # buffer full (more than 2^28 bytes of records): continue in a fresh one
+                more, g2 = self._fetch_text_rest(got, total)
+                del buf
+                return bytes(memoryview(store)[:pos]) + more, got + g2
+            pos += nb
+            got += n.value
+        del buf
+        return memoryview(store)[:pos], got
+
+    def _fetch_text_rest(self, got, total):
+        chunks = []
+        cap = 1 << 26
         buf = C.create_string_buffer(cap)
         n = C.c_uint64(0)
+        g0 = got
         while got < total:
             nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, got, total - got, buf, cap, C.byref(n)))
             if nb <= 0 or n.value == 0:
                 break
             chunks.append(C.string_at(buf, nb))
             got += n.value
-        return b"".join(chunks), got
+        return b"".join(chunks), got - g0
 
     def fetch_records(self, total):
         """(key_hex[], address[], wif[]) of every hit of the last scan, formatted by the library (vgen_cuda_scan_fetch_text)."""

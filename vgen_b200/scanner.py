@@ -28,7 +28,7 @@ class MatchList(collections.abc.Sequence):
 
     def _materialize(self):
         if self._items is None:
-            toks = self._text.decode("ascii").split()
+            toks = str(self._text, "ascii").split()        # bytes or a memoryview of the caller-owned record buffer
             self._items = list(map(GeneratedAddress, toks[1::3], toks[2::3], toks[0::3], itertools.repeat(self._fmt)))
             self._text = None
         return self._items
