@@ -127,11 +127,32 @@ def test_checkpoint_resume(tmp_path):
     # roll the mark back to the 3rd segment and drop the later output: a resumed run completes the set without redoing the first two
     txt = ck.read_text().splitlines()
     cut = start + (2 << 20)
-    ck.write_text("\n".join(l if not l.startswith(("next=", "found=", "operations=")) else
-                            {"n": "next=%064x" % cut, "f": "found=%d" % sum(k < cut for k in keys), "o": "operations=%d" % (2 << 20)}[l[0]] for l in txt) + "\n")
-    out.write_text("".join(l + "\n" for l in out.read_text().splitlines() if int(json.loads(l)["private_key_hex"], 16) < cut))
+    kept = "".join(l + "\n" for l in out.read_text().splitlines() if int(json.loads(l)["private_key_hex"], 16) < cut)
+    ck.write_text("\n".join(l if not l.startswith(("next=", "found=", "operations=", "out_bytes=")) else
+                            {"ne": "next=%064x" % cut, "fo": "found=%d" % sum(k < cut for k in keys), "op": "operations=%d" % (2 << 20),
+                             "ou": "out_bytes=%d" % len(kept)}[l[:2]] for l in txt) + "\n")
+    out.write_text(kept)
     run(*args)
     assert [int(json.loads(l)["private_key_hex"], 16) for l in out.read_text().splitlines()] == keys
+    # a crash between "matches written" and "checkpoint renamed": the output holds matches beyond the mark. The resumed run cuts the
+    # file back to the checkpointed size before it scans those keys again, so nothing is reported twice.
+    full = out.read_text()
+    ck.write_text("\n".join(l if not l.startswith(("next=", "found=", "operations=", "out_bytes=")) else
+                            {"ne": "next=%064x" % cut, "fo": "found=%d" % sum(k < cut for k in keys), "op": "operations=%d" % (2 << 20),
+                             "ou": "out_bytes=%d" % len(kept)}[l[:2]] for l in txt) + "\n")
+    assert len(full) > len(kept)
+    run(*args)
+    assert [int(json.loads(l)["private_key_hex"], 16) for l in out.read_text().splitlines()] == keys
+    # a hit limit reached inside a segment: the mark moves to the last match + 1, so a later run with a larger limit continues there
+    ck2, out2 = tmp_path / "ck2", tmp_path / "out2.jsonl"
+    lim = [a for a in args]
+    lim[lim.index("-c") + 1] = "5"; lim[lim.index(str(out))] = str(out2); lim[lim.index(str(ck))] = str(ck2)
+    run(*lim)
+    assert [int(json.loads(l)["private_key_hex"], 16) for l in out2.read_text().splitlines()] == keys[:5]
+    assert "next=%064x" % (keys[4] + 1) in ck2.read_text() and "found=5" in ck2.read_text()
+    lim[lim.index("-c") + 1] = "8"
+    run(*lim)
+    assert [int(json.loads(l)["private_key_hex"], 16) for l in out2.read_text().splitlines()] == keys[:8]
     # a checkpoint of another scan is refused
     p = run(*[a if a != "^1A" else "^1B" for a in args], ok=False)
     assert p.returncode == 1 and "different scan" in p.stderr

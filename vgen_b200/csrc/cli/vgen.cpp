@@ -288,8 +288,10 @@ void lint_pattern(const std::string &pattern, bool ci, int format) {      // src
     }
 }
 
-// checkpoint file of a range scan: "vgen-checkpoint 1\nstart=<hex>\nend=<hex>\npattern=<p>\nformat=<n>\nnext=<hex>\nfound=<n>\noperations=<n>\n"
-struct Checkpoint { std::string path; Key next{}; uint64_t found = 0, operations = 0; bool resumed = false; };
+// checkpoint file of a range scan: "vgen-checkpoint 1\nstart=<hex>\nend=<hex>\npattern=<p>\nformat=<n>\nnext=<hex>\nfound=<n>\noperations=<n>\nout_bytes=<n>\n"
+// out_bytes: size of the --file output when the checkpoint was written; on resume the file is cut back to it, so that matches
+// written after the last checkpoint (a crash between the two writes) are not reported twice when their segment is scanned again
+struct Checkpoint { std::string path; Key next{}; uint64_t found = 0, operations = 0, out_bytes = 0; bool resumed = false; };
 bool load_checkpoint(Checkpoint &c, const Key &start, const Key &end, const std::string &pattern, int format) {
     std::ifstream f(c.path);
     if (!f) return false;
@@ -300,6 +302,7 @@ bool load_checkpoint(Checkpoint &c, const Key &start, const Key &end, const std:
     if (kv["start"] != key_hex(start) || kv["end"] != key_hex(end) || kv["pattern"] != pattern || kv["format"] != std::to_string(format))
         bail("checkpoint file " + c.path + " belongs to a different scan (range, pattern or format differ)");
     c.next = key_from_hex(kv["next"], "checkpoint"); c.found = strtoull(kv["found"].c_str(), nullptr, 10); c.operations = strtoull(kv["operations"].c_str(), nullptr, 10);
+    c.out_bytes = strtoull(kv["out_bytes"].c_str(), nullptr, 10);
     c.resumed = true;
     return true;
 }
@@ -308,7 +311,7 @@ void save_checkpoint(const Checkpoint &c, const Key &start, const Key &end, cons
     {
         std::ofstream f(tmp, std::ios::trunc);
         f << "vgen-checkpoint 1\nstart=" << key_hex(start) << "\nend=" << key_hex(end) << "\npattern=" << pattern << "\nformat=" << format
-          << "\nnext=" << key_hex(c.next) << "\nfound=" << c.found << "\noperations=" << c.operations << "\n";
+          << "\nnext=" << key_hex(c.next) << "\nfound=" << c.found << "\noperations=" << c.operations << "\nout_bytes=" << c.out_bytes << "\n";
         if (!f) bail("cannot write checkpoint file " + tmp);
     }
     if (rename(tmp.c_str(), c.path.c_str()) != 0) bail("cannot replace checkpoint file " + c.path);
@@ -347,8 +350,15 @@ int run_search(const Args &a, const std::string &pattern, bool ci, int format, b
         } else {
             // resumable scan: segments of --checkpoint-keys keys; after each one its matches are written and the low-water mark saved
             Checkpoint cp; cp.path = a.get("checkpoint"); cp.next = start;
-            if (load_checkpoint(cp, start, end, pattern, format) && !quiet)
-                fprintf(stderr, "Resuming from %s (%s keys done, %llu match(es) so far)\n", key_hex(cp.next).c_str(), with_commas(cp.operations).c_str(), (unsigned long long)cp.found);
+            if (load_checkpoint(cp, start, end, pattern, format)) {
+                if (!quiet) fprintf(stderr, "Resuming from %s (%s keys done, %llu match(es) so far)\n", key_hex(cp.next).c_str(), with_commas(cp.operations).c_str(), (unsigned long long)cp.found);
+                // drop what was written after the last checkpoint: those keys are at or above cp.next and will be scanned again
+                if (w != stdout) {
+                    fflush(w); fseek(w, 0, SEEK_END);
+                    if ((uint64_t)ftell(w) > cp.out_bytes && ftruncate(fileno(w), (off_t)cp.out_bytes) != 0) bail("cannot truncate the output file to its checkpointed size");
+                    fseek(w, 0, SEEK_END);
+                }
+            }
             const uint64_t seg = std::max<uint64_t>(1ull << 20, a.num("checkpoint-keys", 1ull << 36));
             total.operations = cp.operations;
             bool done = cp.resumed && key_cmp(end, cp.next) < 0;
@@ -359,19 +369,29 @@ int run_search(const Args &a, const std::string &pattern, bool ci, int format, b
                 SearchResult part;
                 ps.base = total.operations;
                 scan_once(R, cp.next, &seg_end, count ? count - cp.found : 0, ps, part);
-                const bool complete = !g_stop && (count == 0 || cp.found + part.matches.size() < count);
+                const bool limit_hit = count != 0 && cp.found + part.matches.size() >= count;
+                const bool complete = !g_stop && !limit_hit;
+                const uint64_t seg_ops = part.operations;
                 total.operations += part.operations;
                 part.operations = total.operations; part.elapsed = elapsed();
+                // order: matches out and flushed first, then the checkpoint (renamed into place) with the new mark and output size
                 write_results(w, output, part, pattern, format, quiet, !wrote_header && !cp.resumed);
                 wrote_header = wrote_header || !part.matches.empty();
                 fflush(w);
                 cp.found += part.matches.size();
                 total.matches.insert(total.matches.end(), part.matches.begin(), part.matches.end());
-                if (!complete) break;                                     // interrupted or hit limit reached inside the segment: do not advance the mark
-                done = key_cmp(seg_end, end) == 0;
-                cp.next = key_add64(seg_end, 1);
+                if (complete) { done = key_cmp(seg_end, end) == 0; cp.next = key_add64(seg_end, 1); }
+                else if (limit_hit && !part.matches.empty()) cp.next = key_add64(key_from_hex(part.matches.back().hex, "match"), 1);   // hits are the lowest keys: everything up to the last one is done
+                else {
+                    // interrupted: the library merges windows in key order, so the keys it counted are a prefix of the segment
+                    // (scalar 0 is skipped without being counted)
+                    const bool from_zero = std::all_of(cp.next.begin(), cp.next.end(), [](uint8_t b) { return b == 0; });
+                    cp.next = key_add64(cp.next, seg_ops + (from_zero ? 1 : 0));
+                }
                 cp.operations = total.operations;
+                cp.out_bytes = w != stdout ? (uint64_t)ftell(w) : 0;
                 save_checkpoint(cp, start, end, pattern, format);
+                if (!complete) break;
             }
         }
     }
