@@ -93,6 +93,12 @@ uint64_t vgen_cuda_scan_fetch_records(const vgen_ctx *ctx, uint64_t offset, uint
  * what fits in cap bytes. Returns the number of bytes written (NUL-terminated), *n_written = hits written. */
 int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t max_hits, char *buf, size_t cap, uint64_t *n_written);
 
+/* The same records without a copy: when every hit of the last scan (at most max_hits) has its text record — the scan's confirm
+ * workers build them for all but very dense windows — *text points at the library's own buffer holding all of them back to back
+ * (NUL-terminated, *len bytes) and 1 is returned. The buffer stays valid until the next scan or set_pattern on this context.
+ * Returns 0 (and leaves the outputs untouched) when some record would have to be formatted on demand: use vgen_cuda_scan_fetch_text. */
+int vgen_cuda_scan_text(const vgen_ctx *ctx, const char **text, uint64_t *len);
+
 /* generate_batch (src/gpu.rs:660): hash160 of the compressed public key of n sequential scalars, 20 bytes
  * each; zeros for invalid scalars. */
 int vgen_cuda_hash160_batch(vgen_ctx *ctx, const uint8_t start_be[32], uint64_t n, uint8_t *out20);
@@ -117,7 +123,8 @@ int vgen_cuda_tap_bits(const vgen_ctx *ctx);
 /* Counters of the context, for tests and run reports: out[0] devices, out[1] devices that have dropped out after a CUDA error
  * (their windows were taken over by the others; VGEN_FAULT_INJECT=<device index>:<n> makes the n-th window issue of a device
  * fail that way), out[2] windows taken over from a failed device, out[3] windows whose hits exceeded the per-slot hit buffer and
- * were re-run in pieces, out[4] hit records per slot buffer, out[5] confirm worker threads, out[6..7] reserved (0). */
+ * were re-run in pieces, out[4] hit records per slot buffer, out[5] confirm worker threads, out[6] guarded device buffers and out[7] how many of their
+ * canaries are damaged (both 0 unless the context was created under VGEN_GUARD=1: a 256-byte canary behind every device buffer). */
 void vgen_cuda_stats(const vgen_ctx *ctx, uint64_t out[8]);
 /* bytes the scans of this context copied host->device (start scalars, launch parameters) and device->host (counters, hit records) */
 void vgen_cuda_io_bytes(const vgen_ctx *ctx, uint64_t *h2d, uint64_t *d2h);

@@ -26,8 +26,20 @@ def scan(r, fmt, pat, start, n, count=vg.UNLIMITED):
 
 
 def main():
+    full = "--full" in sys.argv                   # default geometry: 296 CTAs, 77.6 M keys per window
     n = 1 << 18
-    r = vg.GpuRunner(262144)                      # one 256-thread CTA per window
+    r = vg.GpuRunner(0 if full else 262144)       # else one 256-thread CTA per window
+    if full:
+        for fmt in PREFIX:
+            scan(r, fmt, PREFIX[fmt] + ("at" if fmt.startswith("p2pkh") else ""), S, r.batch_size + 12345)
+            if fmt != "p2tr":
+                scan(r, fmt, SUFFIX[fmt] if fmt != "p2pkh-uncompressed" else "99$", S, r.batch_size // 4)
+        st = r.stats()
+        print("stats", st, flush=True)
+        assert st["damaged_guards"] == 0, st
+        r.close()
+        print("SANITIZE_DRIVER_OK")
+        return
     for fmt in PREFIX:
         scan(r, fmt, PREFIX[fmt], S, n)
         scan(r, fmt, SUFFIX[fmt], S, n)
@@ -50,7 +62,9 @@ def main():
         assert len(r.digest_batch(fmt, S + 7, 1025)) == 1025 * (32 if fmt == "p2tr" else 20)
     r.dispatch_p2tr(S, 0, n=777)
     assert len(r.await_result_p2tr(0)[0]) == 777
-    print("stats", r.stats(), flush=True)
+    st = r.stats()
+    print("stats", st, flush=True)
+    assert st["damaged_guards"] == 0, st
     r.close()
     print("SANITIZE_DRIVER_OK")
 

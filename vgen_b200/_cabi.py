@@ -35,6 +35,7 @@ SYMBOLS = {
     "vgen_cuda_scan_fetch_hits": (C.c_uint64, [C.c_void_p, C.c_uint64, C.POINTER(VgenHit), C.c_uint64]),
     "vgen_cuda_scan_fetch_records": (C.c_uint64, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "vgen_cuda_scan_fetch_text": (C.c_int64, [C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_size_t, C.POINTER(C.c_uint64)]),
+    "vgen_cuda_scan_text": (C.c_int, [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64)]),
     "vgen_cuda_hash160_batch": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.c_void_p]),
     "vgen_cuda_digest_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint32]),
     "vgen_cuda_bench_resident": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),

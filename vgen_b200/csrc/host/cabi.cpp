@@ -173,6 +173,13 @@ int64_t vgen_cuda_scan_fetch_text(const vgen_ctx *ctx, uint64_t offset, uint64_t
     *n_written = n;
     return (int64_t)pos;
 }
+int vgen_cuda_scan_text(const vgen_ctx *ctx, const char **text, uint64_t *len) {
+    if (!ctx || !text || !len || !ctx->all_text) return 0;
+    // hits beyond max_hits were cut off the hit list; their records are still at the end of the blob: stop at the last kept hit
+    const uint64_t n = ctx->hits.empty() ? 0 : ctx->hits.back().text_off + ctx->hits.back().text_len;
+    *text = ctx->text.c_str(); *len = n;
+    return 1;
+}
 int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32], uint64_t n, uint8_t *out, uint32_t stride) {
     if (!ctx || !start_be || (!out && n)) return VGEN_ERR_INVALID_ARG;
     std::string err;
@@ -202,6 +209,8 @@ void vgen_cuda_stats(const vgen_ctx *ctx, uint64_t out[8]) {
     const vg::Engine &e = ctx->engine;
     out[0] = (uint64_t)e.n_devices(); out[1] = (uint64_t)e.n_failed_devices(); out[2] = e.requeued_windows.load();
     out[3] = e.overflow_rescans.load(); out[4] = e.hit_cap(); out[5] = e.pool_threads();
+    auto g = const_cast<vg::Engine &>(e).check_guards();
+    out[6] = g.first; out[7] = g.second;
 }
 int vgen_cuda_lane_count(const vgen_ctx *ctx) { return ctx ? ctx->engine.n_lanes() : 0; }
 int vgen_cuda_tap_bits(const vgen_ctx *ctx) { return ctx ? (int)ctx->engine.tap_bits() : 0; }

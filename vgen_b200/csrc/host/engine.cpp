@@ -61,6 +61,29 @@ std::future<HitBatch> WorkerPool::submit(std::function<HitBatch()> fn) {
 
 Engine::~Engine() { destroy(); }
 
+static const size_t kGuardBytes = 256;
+cudaError_t Engine::dmalloc(void **p, size_t bytes, int device) {
+    if (!guard_) return cudaMalloc(p, bytes);
+    const size_t padded = (bytes + 15) & ~(size_t)15;
+    cudaError_t e = cudaMalloc(p, padded + kGuardBytes);
+    if (e != cudaSuccess) return e;
+    e = cudaMemset((uint8_t *)*p + padded, 0xA5, kGuardBytes);
+    std::lock_guard<std::mutex> g(guards_mu_);
+    guards_.push_back({device, (uint8_t *)*p + padded});
+    return e;
+}
+std::pair<uint64_t, uint64_t> Engine::check_guards() {
+    std::lock_guard<std::mutex> g(guards_mu_);
+    uint64_t bad = 0;
+    uint8_t host[kGuardBytes];
+    for (auto &G : guards_) {
+        if (cudaSetDevice(G.device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess ||
+            cudaMemcpy(host, G.at, kGuardBytes, cudaMemcpyDeviceToHost) != cudaSuccess) { bad++; continue; }
+        for (size_t i = 0; i < kGuardBytes; i++) if (host[i] != 0xA5) { bad++; break; }
+    }
+    return {(uint64_t)guards_.size(), bad};
+}
+
 int Engine::lanes_per_device() {
     const char *e = getenv("VGEN_LANES_PER_GPU");       // tuning override
     int n = e ? atoi(e) : 2;
@@ -104,6 +127,7 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
     else devs.push_back(0);
     for (int d : devs) if (d < 0 || d >= count) { err = "invalid device index " + std::to_string(d); return false; }
     half_ = 512;
+    guard_ = getenv("VGEN_GUARD") != nullptr;
     int min_sm = 1 << 30;
     for (int d : devs) {
         cudaDeviceProp prop;
@@ -134,22 +158,22 @@ bool Engine::create(const int *devices, int n_devices, uint32_t hint, std::strin
     for (int lv = 0; lv < (int)levels_.size(); lv++) if (levels_[lv].window <= cap) rescan_level_ = lv;
     for (auto &D : devices_) {
         CK(cudaSetDevice(D.device));
-        CK(cudaMalloc(&D.d_pow2, (size_t)VG_GTABLE_WORDS * 4));       // pow2[256] + win8[32][256] (ec.cuh)
-        CK(cudaMalloc(&D.d_gtab, (size_t)half_ * 16 * 4));
+        CK(dmalloc((void **)&D.d_pow2, (size_t)VG_GTABLE_WORDS * 4, D.device));       // pow2[256] + win8[32][256] (ec.cuh)
+        CK(dmalloc((void **)&D.d_gtab, (size_t)half_ * 16 * 4, D.device));
     }
     for (auto &L : lanes_) {
         CK(cudaSetDevice(L.device));
         CK(cudaStreamCreateWithFlags(&L.stream, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&L.copy_stream, cudaStreamNonBlocking));
-        CK(cudaMalloc(&L.d_centers, (size_t)16 * F.threads * 4));
-        CK(cudaMalloc(&L.d_scratch, (size_t)(half_ + 1) * 8 * F.threads * 4));
-        CK(cudaMalloc(&L.d_base8, 64));
-        CK(cudaMalloc(&L.d_stride_pts, 16 * 4));
+        CK(dmalloc((void **)&L.d_centers, (size_t)16 * F.threads * 4, L.device));
+        CK(dmalloc((void **)&L.d_scratch, (size_t)(half_ + 1) * 8 * F.threads * 4, L.device));
+        CK(dmalloc((void **)&L.d_base8, 64, L.device));
+        CK(dmalloc((void **)&L.d_stride_pts, 16 * 4, L.device));
         for (auto &S : L.slot) {
-            CK(cudaMalloc(&S.d_hits, (size_t)hit_cap_ * sizeof(vg_hit_rec)));
-            CK(cudaMalloc(&S.d_counters, kCounterWords * 4));
-            CK(cudaMalloc(&S.d_degen, (size_t)F.threads * 4));
-            CK(cudaMalloc(&S.d_base8, 32));
+            CK(dmalloc((void **)&S.d_hits, (size_t)hit_cap_ * sizeof(vg_hit_rec), L.device));
+            CK(dmalloc((void **)&S.d_counters, kCounterWords * 4, L.device));
+            CK(dmalloc((void **)&S.d_degen, (size_t)F.threads * 4, L.device));
+            CK(dmalloc((void **)&S.d_base8, 32, L.device));
             CK(cudaHostAlloc(&S.h_counters, kCounterWords * 4, cudaHostAllocDefault));
             CK(cudaHostAlloc(&S.h_hits, (size_t)std::min(hit_cap_, kStageRecords) * sizeof(vg_hit_rec), cudaHostAllocDefault));
             CK(cudaEventCreateWithFlags(&S.done, cudaEventDisableTiming));
@@ -208,8 +232,8 @@ bool Engine::upload_dfa(std::string &err) {
         if (D.failed) continue;
         CK(cudaSetDevice(D.device));
         // buffers are kept and reused when the new tables fit: cudaFree / cudaMalloc synchronise the device
-        if (D.dfa_table_cap < tb) { if (D.d_dfa_table) cudaFree(D.d_dfa_table); D.d_dfa_table = nullptr; CK(cudaMalloc(&D.d_dfa_table, std::max<size_t>(tb, 4096))); D.dfa_table_cap = std::max<size_t>(tb, 4096); }
-        if (D.dfa_accept_cap < ab) { if (D.d_dfa_accept) cudaFree(D.d_dfa_accept); D.d_dfa_accept = nullptr; CK(cudaMalloc(&D.d_dfa_accept, std::max<size_t>(ab, 1024))); D.dfa_accept_cap = std::max<size_t>(ab, 1024); }
+        if (D.dfa_table_cap < tb) { if (D.d_dfa_table) cudaFree(D.d_dfa_table); D.d_dfa_table = nullptr; CK(dmalloc((void **)&D.d_dfa_table, std::max<size_t>(tb, 4096), D.device)); D.dfa_table_cap = std::max<size_t>(tb, 4096); }
+        if (D.dfa_accept_cap < ab) { if (D.d_dfa_accept) cudaFree(D.d_dfa_accept); D.d_dfa_accept = nullptr; CK(dmalloc((void **)&D.d_dfa_accept, std::max<size_t>(ab, 1024), D.device)); D.dfa_accept_cap = std::max<size_t>(ab, 1024); }
         CK(cudaMemcpy(D.d_dfa_table, tbuf.data(), tb, cudaMemcpyHostToDevice));
         CK(cudaMemcpy(D.d_dfa_accept, abuf.data(), ab, cudaMemcpyHostToDevice));
     }
@@ -240,7 +264,7 @@ bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
     for (auto &L : lanes_) {
         if (L.d_points || devices_[L.dev].failed) continue;
         CK(cudaSetDevice(L.device));
-        CK(cudaMalloc(&L.d_points, (size_t)F.window * 64));
+        CK(dmalloc((void **)&L.d_points, (size_t)F.window * 64, L.device));
     }
     if (tap_bits_ != 0 && (tap_bits_ >= want || getenv("VGEN_TAP_BITS"))) return true;
     for (auto &D : devices_) {            // a big table needs room: fall back to the small one on a crowded device
@@ -259,7 +283,7 @@ bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
         if (D.failed) continue;
         CK(cudaSetDevice(D.device));
         if (D.d_tap_table) { CK(cudaFree(D.d_tap_table)); D.d_tap_table = nullptr; }
-        CK(cudaMalloc(&D.d_tap_table, tap_table_bytes(want)));
+        CK(dmalloc((void **)&D.d_tap_table, tap_table_bytes(want), D.device));
         CK(launch_build_tap_table(D.d_tap_table, want, D.d_pow2, lanes_[D.lanes[0]].stream));
         launches++;
     }
@@ -328,6 +352,7 @@ void Engine::fill_params(Lane &L, Slot &S, const uint32_t *stride16, vg_scan_par
     P.hits = S.d_hits; P.hit_count = S.d_counters; P.hit_cap = hit_cap_;
     P.degen_list = S.d_degen; P.degen_count = S.d_counters + 1; P.degen_cap = V.threads;
     P.points = L.d_points; P.tap_table = D.d_tap_table; P.tap_bits = tap_bits_;
+    P.violations = S.d_counters + 2;
     P.m = lp_.dev;
     P.m.dfa.table = D.d_dfa_table; P.m.dfa.accept = D.d_dfa_accept;
     P.dfa_smem_bytes = (P.m.kind == VG_MATCH_DFA || P.m.confirm_dfa) ? dfa_smem_bytes(P.m.dfa) : 0;
@@ -454,6 +479,10 @@ bool Engine::harvest(Lane &L, Slot &S, int fmt, ScanRun &R, Harvest &out, std::s
     CK(cudaEventSynchronize(S.done));
     // degenerate batches of the window just finished + record fetch; used for the window itself and for rescan pieces
     auto finish = [&](uint32_t &n_hits) -> bool {
+        if (S.h_counters[2]) {      // only a checked build (-DVG_CHECKED) ever writes here
+            err = "device bounds check " + std::to_string(S.h_counters[2]) + " failed (" + std::to_string(S.h_counters[3]) + " times)";
+            return false;
+        }
         n_hits = S.h_counters[0];
         const uint32_t n_degen = S.h_counters[1];
         if (n_degen && fmt == VG_FMT_P2TR) {

@@ -122,6 +122,8 @@ public:
     std::atomic<uint64_t> h2d_bytes{0}, d2h_bytes{0};   // bytes copied host->device / device->host by scans so far
     std::atomic<uint64_t> overflow_rescans{0};          // windows whose hits exceeded the hit buffer and were re-run in pieces
     std::atomic<uint64_t> requeued_windows{0};          // windows taken over from a failed device
+    // VGEN_GUARD=1 (tools/check_build.sh): every device buffer gets a 256-byte canary behind it; returns (regions, corrupted)
+    std::pair<uint64_t, uint64_t> check_guards();
 private:
     struct ScanRun;
     struct Harvest;
@@ -133,6 +135,11 @@ private:
     bool fetch_records(Lane &L, Slot &S, uint32_t n_hits, const U256 &base, uint64_t limit, Harvest &out, std::string &err);
     void device_worker(ScanRun &R, int dev_index);
     bool upload_dfa(std::string &err);
+    cudaError_t dmalloc(void **p, size_t bytes, int device);       // cudaMalloc (+ canary under VGEN_GUARD)
+    struct Guard { int device; uint8_t *at; };
+    std::vector<Guard> guards_;
+    std::mutex guards_mu_;
+    bool guard_ = false;
     bool ensure_taproot(uint64_t keys_hint, std::string &err);
     uint32_t tap_bits_ = 0;                      // window width of the P2TR table currently built (0 = none)
     void destroy();

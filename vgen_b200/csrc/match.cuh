@@ -25,10 +25,17 @@ struct vg_dfa_view {
     const uint8_t *sym;        // [64] alphabet index -> class (vg_dfa_dev::sym_class)
     const uint32_t *poly = nullptr;   // Bech32 checksum table in shared memory (vg_bech32_fill_table), or null: stepwise polymod
     const uint32_t *b58 = nullptr;    // radix-conversion table in shared memory (vg_b58_fill_table), or null: long division
+    uint32_t n_table = 0, n_accept = 0;   // entries of table / accept (checked builds)
+    uint32_t *viol = nullptr;             // vg_scan_params::violations (checked builds)
 };
 
 VG_DEV uint32_t vg_dfa_step(const vg_dfa_view &v, uint32_t n_classes, uint32_t st, uint32_t cls) {
+    VG_ASSERT_AT(v.viol, st * n_classes + cls < v.n_table && cls < n_classes, 7);
     return v.table[st * n_classes + cls];
+}
+VG_DEV bool vg_dfa_accepts(const vg_dfa_view &v, uint32_t st) {
+    VG_ASSERT_AT(v.viol, st < v.n_accept, 8);
+    return v.accept[st] != 0;
 }
 
 // ---- SHA-256 of exactly 32 bytes given as 8 big-endian words (second half of the Base58Check checksum) ----
@@ -139,7 +146,7 @@ VG_DEV bool vg_match_base58check_tab(const vg_matcher_dev &m, const vg_dfa_view 
             if (started) st = vg_dfa_step(v, nc, st, v.sym[ds[k]]);
         }
     }
-    return v.accept[st] != 0;
+    return vg_dfa_accepts(v, st);
 }
 
 // Base58Check(version || h160): runs the DFA over the address symbols. dg = h160 as little-endian words.
@@ -205,7 +212,7 @@ VG_DEV bool vg_match_base58check(const vg_matcher_dev &m, const vg_dfa_view &v, 
             if (started) st = vg_dfa_step(v, nc, st, v.sym[ds[k]]);
         }
     }
-    return v.accept[st] != 0;
+    return vg_dfa_accepts(v, st);
 }
 
 // ---- Bech32 / Bech32m (BIP173 / BIP350) ----
@@ -290,7 +297,7 @@ VG_DEV bool vg_match_segwit(const vg_matcher_dev &m, const vg_dfa_view &v, const
         chk ^= final_xor;
     }
     VG_UNROLL for (int i = 0; i < 6; i++) st = vg_dfa_step(v, nc, st, v.sym[(chk >> (5 * (5 - i))) & 31u]);
-    return v.accept[st] != 0;
+    return vg_dfa_accepts(v, st);
 }
 // P2WPKH: Bech32, witness v0, 20-byte program (32 symbols). dg = the program bytes as little-endian words.
 VG_DEV bool vg_match_p2wpkh(const vg_matcher_dev &m, const vg_dfa_view &v, const uint32_t dg[VG_DIGEST_WORDS]) {
@@ -350,7 +357,7 @@ VG_DEV bool vg_match_eth(const vg_matcher_dev &m, const vg_dfa_view &v, const ui
         st = vg_dfa_step(v, nc, st, v.sym[s0]);
         st = vg_dfa_step(v, nc, st, v.sym[s1]);
     }
-    return v.accept[st] != 0;
+    return vg_dfa_accepts(v, st);
 }
 
 template <int FMT>

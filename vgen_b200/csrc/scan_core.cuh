@@ -14,6 +14,17 @@
 #include "hash.cuh"
 #include "scan_types.h"
 
+// Device-side bounds checks of the checked build (-DVG_CHECKED): a failed check records its code in P.violations and the host
+// turns it into an error (engine.cpp harvest). Compiled out of the product build. Codes: 1 thread id, 2 scratch index, 3 table
+// index, 4 hit slot, 5 degenerate-list slot, 6 point-buffer index, 7 DFA table index, 8 DFA accept index, 9 shared-memory size,
+// 10 fixed-base table index, 11 dump index.
+#if defined(VG_CHECKED) && !defined(VG_HOST_EMU)
+#define VG_ASSERT_AT(viol, cond, code) do { if (!(cond) && (viol)) { atomicCAS((viol), 0u, (uint32_t)(code)); atomicAdd((viol) + 1, 1u); } } while (0)
+#else
+#define VG_ASSERT_AT(viol, cond, code) ((void)0)
+#endif
+#define VG_ASSERT(P, cond, code) VG_ASSERT_AT((P).violations, cond, code)
+
 // digest words of N points at once (T = uint32_t or vw<N>); xv / yv = little-endian limbs of canonical coordinates
 template <int FMT, class T>
 VG_DEV void vg_digest_lanes(T dg[VG_DIGEST_WORDS], const T xv[8], const T yv[8]) {
@@ -84,6 +95,7 @@ __device__ __forceinline__ void vg_emit_hit(const vg_scan_params &P, bool is_hit
     if (is_hit) {
         uint32_t slot = base + __popc(mask & ((1u << lane) - 1u));
         if (slot < P.hit_cap) {
+            VG_ASSERT(P, idx < (unsigned long long)P.n_threads * 2ull * P.half, 4);
             vg_hit_rec *h = P.hits + slot;
             h->idx_lo = (uint32_t)idx; h->idx_hi = (uint32_t)(idx >> 32);
             #pragma unroll
@@ -102,6 +114,7 @@ VG_DEV void vg_finish_point(const vg_scan_params &P, const vg_dfa_view &dv, cons
     valid = valid && idx < P.limit;
     if (MODE == VG_MODE_DUMP) {
         if (valid) {
+            VG_ASSERT(P, P.dump != nullptr && idx < P.limit, 11);
             uint8_t *o = P.dump + idx * P.dump_stride;
             for (uint32_t b = 0; b < P.dump_stride; b++) {
                 uint32_t wsel = 0;
@@ -123,6 +136,7 @@ VG_DEV void vg_process_point(const vg_scan_params &P, const vg_dfa_view &dv, fe 
         valid = valid && idx < P.limit;
         fe ny; fe_neg(ny, y); fe_canon(ny);
         const bool odd = (y.v[0] & 1u) != 0;
+        VG_ASSERT(P, P.points != nullptr && idx < (unsigned long long)P.n_threads * 2ull * P.half, 6);
         uint32_t *o = P.points + idx * 16;
         VG_UNROLL for (int l = 0; l < 8; l++) { o[l] = valid ? x.v[l] : 0u; o[8 + l] = valid ? (odd ? ny.v[l] : y.v[l]) : 0u; }
         return;
@@ -177,6 +191,7 @@ VG_DEV void vg_process_pair(const vg_scan_params &P, const vg_dfa_view &dv, fe &
 template <int FMT, int MODE>
 VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const uint32_t *gtab, uint32_t tid) {
     const uint32_t T = P.n_threads, H = P.half;
+    VG_ASSERT(P, tid < T, 1);
     fe cx, cy, sx, sy;
     VG_LOAD_FE(cx, P.centers + tid, T);
     VG_LOAD_FE(cy, P.centers + (size_t)8 * T + tid, T);
@@ -261,6 +276,7 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const
 #else
         uint32_t slot = atomicAdd(P.degen_count, 1u);
 #endif
+        VG_ASSERT(P, slot < P.degen_cap, 5);
         if (slot < P.degen_cap) P.degen_list[slot] = tid;
     }
     VG_STORE_FE(P.centers + tid, T, nx);

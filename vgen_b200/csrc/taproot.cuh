@@ -104,7 +104,8 @@ VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t j, uint32_t bits) {
 // q.y is then not computed for the top window (VG_TAP_LAST_NO_Y): only q.x and q.z are meaningful.
 // FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
 template <bool FAST>
-VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true) {
+VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true, uint32_t *viol = nullptr) {
+    (void)viol;
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
     bool special = false, affine = true;        // affine: q.z is still 1
     const uint32_t n_win = vg_tap_windows(bits), mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
@@ -117,6 +118,7 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
 #endif
         const uint32_t v = vg_tap_digit(t, j, bits);
         if (v == 0 || !active || special) continue;
+        VG_ASSERT_AT(viol, j < n_win && v <= mask, 10);
         const uint32_t *e = tab + ((size_t)j * ((size_t)mask + 1) + v) * 16;
         fe bx, by;
 #ifdef VG_HOST_EMU
@@ -154,6 +156,7 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
 #if VG_TAP_SYNC == 1 && !defined(VG_HOST_EMU)
         __syncthreads();      // re-align the CTA's warps once per key (instruction-fetch sharing, see VG_SYNC_ITER in scan_core.cuh)
 #endif
+        VG_ASSERT(P, first + (unsigned long long)k < (unsigned long long)P.n_threads * 2ull * P.half, 6);
         const uint32_t *p = P.points + (first + (unsigned long long)k) * 16;
         fe px, py;
 #ifdef VG_HOST_EMU
@@ -173,7 +176,7 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
             ok = ok && vg_tweak_is_valid(t);
             gej_t q;
             // all threads walk the table loop together (barriers inside); invalid keys skip the additions
-            if (!vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits, ok) && ok)
+            if (!vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits, ok, P.violations) && ok)
                 ok = vg_tap_output_key_slow(q, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
             if (ok) { X[k] = q.x; fe_sqr_fast(z2, q.z); }
         }

@@ -177,7 +177,8 @@ class GpuRunner:
         """dict of the context's counters (vgen_cuda_stats): devices, failed_devices, requeued_windows, overflow_rescans, hit_cap, confirm_threads."""
         a = (C.c_uint64 * 8)()
         self._lib.vgen_cuda_stats(self._ctx, a)
-        return dict(devices=a[0], failed_devices=a[1], requeued_windows=a[2], overflow_rescans=a[3], hit_cap=a[4], confirm_threads=a[5])
+        return dict(devices=a[0], failed_devices=a[1], requeued_windows=a[2], overflow_rescans=a[3], hit_cap=a[4], confirm_threads=a[5],
+                    guarded_buffers=a[6], damaged_guards=a[7])
 
     def io_bytes(self):
         a, b = C.c_uint64(0), C.c_uint64(0)
@@ -215,6 +216,10 @@ class GpuRunner:
         ONE caller-owned buffer. Returns (bytes-like, hits)."""
         if total <= 0:
             return b"", 0
+        # fast path: the scan's confirm workers already built every record; one copy out of the library's buffer
+        ptr, ln = C.c_void_p(), C.c_uint64(0)
+        if self._lib.vgen_cuda_scan_text(self._ctx, C.cast(C.byref(ptr), C.POINTER(C.c_char_p)), C.byref(ln)):
+            return C.string_at(ptr, ln.value), total
         cap = min(total * 227 + 1, 1 << 28)               # 227 = the library's bound for one record
         store = bytearray(cap)
         buf = (C.c_char * cap).from_buffer(store)
