@@ -15,6 +15,7 @@
 
 #ifdef VG_HOST_EMU
 #define VG_DEV static inline
+#define VG_DEVM inline                 /* member functions */
 #define VG_COLD static inline
 static thread_local uint32_t vg_cc = 0;
 static inline uint32_t vg_add_cc(uint32_t a, uint32_t b, uint32_t cin) { uint64_t t = (uint64_t)a + b + cin; vg_cc = (uint32_t)(t >> 32); return (uint32_t)t; }
@@ -34,6 +35,7 @@ static inline uint32_t vg_mad_hi_cc(uint32_t a, uint32_t b, uint32_t c, uint32_t
 #define VG_UNROLL
 #else
 #define VG_DEV __device__ __forceinline__
+#define VG_DEVM __device__ __forceinline__
 #define VG_COLD static __device__ __noinline__
 #define ADD_CC(r, a, b) asm volatile("add.cc.u32 %0,%1,%2;" : "=r"(r) : "r"(a), "r"(b))
 #define ADDC_CC(r, a, b) asm volatile("addc.cc.u32 %0,%1,%2;" : "=r"(r) : "r"(a), "r"(b))

@@ -119,8 +119,14 @@ template <class T> VG_DEV void sha256_iv(T st[8]) {
 // on the ALU pipe, the two plain shifts and w[i-16] + w[i-7] on the multiplier pipe.
 // CMASK: bit i set = message word i is a compile-time constant (padding), so K + w folds and must not be forced
 // through an IMAD.
-template <uint32_t CMASK, class T>
-VG_DEV void sha256_compress(T st[8], T w[16]) {
+// Hooks. The hashes below are ~2,300 add/logic/shift instructions in a row: pure ALU-pipe work. A caller may pass a hook object
+// whose at(k) is called at fixed points between rounds (k = 0..7 after every 8th SHA-256 round, k = 8..17 after every 16th
+// RIPEMD-160 step); the walk kernel uses it to issue the NEXT point's field multiplications (multiplier-pipe work) in between
+// (scan_core.cuh VG_PIPELINE), so that one warp feeds both pipes instead of taking turns. k is a compile-time constant after
+// unrolling, so an at() that tests k folds to nothing where it does nothing.
+struct vg_no_hook { VG_DEVM void at(int) const {} };
+template <uint32_t CMASK, class T, class Hook>
+VG_DEV void sha256_compress(T st[8], T w[16], Hook &hk) {
     T a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
     VG_UNROLL for (int i = 0; i < 64; i++) {
         if (i >= 16) {
@@ -137,13 +143,16 @@ VG_DEV void sha256_compress(T st[8], T w[16]) {
         T S0 = vg_rotr(a, 2) ^ vg_rotr(a, 13) ^ (VG_SHA_ROT_FMA >= 2 ? vg_rotl_f(a, 10) : vg_rotr(a, 22));
         T mj = (a & b) | (c & (a | b));
         h = g; g = f; f = e; e = vg_addf(d, t1); d = c; c = b; b = a; a = t1 + S0 + mj;
+        if ((i & 7) == 7) hk.at(i >> 3);
     }
     st[0] = vg_addf(st[0], a); st[1] = vg_addf(st[1], b); st[2] = vg_addf(st[2], c); st[3] = vg_addf(st[3], d);
     st[4] = vg_addf(st[4], e); st[5] = vg_addf(st[5], f); st[6] = vg_addf(st[6], g); st[7] = vg_addf(st[7], h);
 }
+template <uint32_t CMASK, class T>
+VG_DEV void sha256_compress(T st[8], T w[16]) { vg_no_hook nh; sha256_compress<CMASK, T, vg_no_hook>(st, w, nh); }
 // SHA-256(prefix || X) for a 33-byte compressed key; xv = the 8 little-endian limbs of a canonical field element
-template <class T>
-VG_DEV void sha256_pub33(T out[8], const T &prefix, const T xv[8]) {
+template <class T, class Hook>
+VG_DEV void sha256_pub33(T out[8], const T &prefix, const T xv[8], Hook &hk) {
     T w[16];
     w[0] = (prefix << 24) | (xv[7] >> 8);
     VG_UNROLL for (int k = 1; k < 8; k++) w[k] = vg_shf_l(xv[7 - k], xv[8 - k], 24);
@@ -151,8 +160,10 @@ VG_DEV void sha256_pub33(T out[8], const T &prefix, const T xv[8]) {
     VG_UNROLL for (int k = 9; k < 15; k++) vg_splat(w[k], 0u);
     vg_splat(w[15], 33 * 8);
     sha256_iv(out);
-    sha256_compress<0xFE00u>(out, w);
+    sha256_compress<0xFE00u, T, Hook>(out, w, hk);
 }
+template <class T>
+VG_DEV void sha256_pub33(T out[8], const T &prefix, const T xv[8]) { vg_no_hook nh; sha256_pub33<T, vg_no_hook>(out, prefix, xv, nh); }
 // SHA-256(04 || X || Y) for a 65-byte uncompressed key (two blocks)
 template <class T>
 VG_DEV void sha256_pub65(T out[8], const T xv[8], const T yv[8]) {
@@ -190,8 +201,8 @@ VG_DEV void sha256_short(T out[8], const T *m) {
 #define VG_RMD_STEP(F, a, b, c, d, e, xw, s) \
     a = vg_rotl(a + F(b, c, d) + (xw), s) + e; c = vg_rotl_f(c, 10);
 
-template <class T>
-VG_DEV void ripemd160_32(T out[5], const T sha[8]) {
+template <class T, class Hook>
+VG_DEV void ripemd160_32(T out[5], const T sha[8], Hook &hk) {
     T x[16];
     VG_UNROLL for (int i = 0; i < 8; i++) x[i] = vg_bswap(sha[i]);
     const uint32_t pad[8] = {0x80u, 0, 0, 0, 0, 0, 256u, 0};
@@ -207,59 +218,73 @@ VG_DEV void ripemd160_32(T out[5], const T sha[8]) {
     L(VG_RMD_F0,b,c,d,e,a,4,5,0u) L(VG_RMD_F0,a,b,c,d,e,5,8,0u) L(VG_RMD_F0,e,a,b,c,d,6,7,0u) L(VG_RMD_F0,d,e,a,b,c,7,9,0u)
     L(VG_RMD_F0,c,d,e,a,b,8,11,0u) L(VG_RMD_F0,b,c,d,e,a,9,13,0u) L(VG_RMD_F0,a,b,c,d,e,10,14,0u) L(VG_RMD_F0,e,a,b,c,d,11,15,0u)
     L(VG_RMD_F0,d,e,a,b,c,12,6,0u) L(VG_RMD_F0,c,d,e,a,b,13,7,0u) L(VG_RMD_F0,b,c,d,e,a,14,9,0u) L(VG_RMD_F0,a,b,c,d,e,15,8,0u)
+    hk.at(8);
 #define K1 0x5A827999u
     L(VG_RMD_F1,e,a,b,c,d,7,7,K1) L(VG_RMD_F1,d,e,a,b,c,4,6,K1) L(VG_RMD_F1,c,d,e,a,b,13,8,K1) L(VG_RMD_F1,b,c,d,e,a,1,13,K1)
     L(VG_RMD_F1,a,b,c,d,e,10,11,K1) L(VG_RMD_F1,e,a,b,c,d,6,9,K1) L(VG_RMD_F1,d,e,a,b,c,15,7,K1) L(VG_RMD_F1,c,d,e,a,b,3,15,K1)
     L(VG_RMD_F1,b,c,d,e,a,12,7,K1) L(VG_RMD_F1,a,b,c,d,e,0,12,K1) L(VG_RMD_F1,e,a,b,c,d,9,15,K1) L(VG_RMD_F1,d,e,a,b,c,5,9,K1)
     L(VG_RMD_F1,c,d,e,a,b,2,11,K1) L(VG_RMD_F1,b,c,d,e,a,14,7,K1) L(VG_RMD_F1,a,b,c,d,e,11,13,K1) L(VG_RMD_F1,e,a,b,c,d,8,12,K1)
+    hk.at(9);
 #define K2 0x6ED9EBA1u
     L(VG_RMD_F2,d,e,a,b,c,3,11,K2) L(VG_RMD_F2,c,d,e,a,b,10,13,K2) L(VG_RMD_F2,b,c,d,e,a,14,6,K2) L(VG_RMD_F2,a,b,c,d,e,4,7,K2)
     L(VG_RMD_F2,e,a,b,c,d,9,14,K2) L(VG_RMD_F2,d,e,a,b,c,15,9,K2) L(VG_RMD_F2,c,d,e,a,b,8,13,K2) L(VG_RMD_F2,b,c,d,e,a,1,15,K2)
     L(VG_RMD_F2,a,b,c,d,e,2,14,K2) L(VG_RMD_F2,e,a,b,c,d,7,8,K2) L(VG_RMD_F2,d,e,a,b,c,0,13,K2) L(VG_RMD_F2,c,d,e,a,b,6,6,K2)
     L(VG_RMD_F2,b,c,d,e,a,13,5,K2) L(VG_RMD_F2,a,b,c,d,e,11,12,K2) L(VG_RMD_F2,e,a,b,c,d,5,7,K2) L(VG_RMD_F2,d,e,a,b,c,12,5,K2)
+    hk.at(10);
 #define K3 0x8F1BBCDCu
     L(VG_RMD_F3,c,d,e,a,b,1,11,K3) L(VG_RMD_F3,b,c,d,e,a,9,12,K3) L(VG_RMD_F3,a,b,c,d,e,11,14,K3) L(VG_RMD_F3,e,a,b,c,d,10,15,K3)
     L(VG_RMD_F3,d,e,a,b,c,0,14,K3) L(VG_RMD_F3,c,d,e,a,b,8,15,K3) L(VG_RMD_F3,b,c,d,e,a,12,9,K3) L(VG_RMD_F3,a,b,c,d,e,4,8,K3)
     L(VG_RMD_F3,e,a,b,c,d,13,9,K3) L(VG_RMD_F3,d,e,a,b,c,3,14,K3) L(VG_RMD_F3,c,d,e,a,b,7,5,K3) L(VG_RMD_F3,b,c,d,e,a,15,6,K3)
     L(VG_RMD_F3,a,b,c,d,e,14,8,K3) L(VG_RMD_F3,e,a,b,c,d,5,6,K3) L(VG_RMD_F3,d,e,a,b,c,6,5,K3) L(VG_RMD_F3,c,d,e,a,b,2,12,K3)
+    hk.at(11);
 #define K4 0xA953FD4Eu
     L(VG_RMD_F4,b,c,d,e,a,4,9,K4) L(VG_RMD_F4,a,b,c,d,e,0,15,K4) L(VG_RMD_F4,e,a,b,c,d,5,5,K4) L(VG_RMD_F4,d,e,a,b,c,9,11,K4)
     L(VG_RMD_F4,c,d,e,a,b,7,6,K4) L(VG_RMD_F4,b,c,d,e,a,12,8,K4) L(VG_RMD_F4,a,b,c,d,e,2,13,K4) L(VG_RMD_F4,e,a,b,c,d,10,12,K4)
     L(VG_RMD_F4,d,e,a,b,c,14,5,K4) L(VG_RMD_F4,c,d,e,a,b,1,12,K4) L(VG_RMD_F4,b,c,d,e,a,3,13,K4) L(VG_RMD_F4,a,b,c,d,e,8,14,K4)
     L(VG_RMD_F4,e,a,b,c,d,11,11,K4) L(VG_RMD_F4,d,e,a,b,c,6,8,K4) L(VG_RMD_F4,c,d,e,a,b,15,5,K4) L(VG_RMD_F4,b,c,d,e,a,13,6,K4)
+    hk.at(12);
     // right line
 #define J0 0x50A28BE6u
     L(VG_RMD_F4,A,B,C,D,E,5,8,J0) L(VG_RMD_F4,E,A,B,C,D,14,9,J0) L(VG_RMD_F4,D,E,A,B,C,7,9,J0) L(VG_RMD_F4,C,D,E,A,B,0,11,J0)
     L(VG_RMD_F4,B,C,D,E,A,9,13,J0) L(VG_RMD_F4,A,B,C,D,E,2,15,J0) L(VG_RMD_F4,E,A,B,C,D,11,15,J0) L(VG_RMD_F4,D,E,A,B,C,4,5,J0)
     L(VG_RMD_F4,C,D,E,A,B,13,7,J0) L(VG_RMD_F4,B,C,D,E,A,6,7,J0) L(VG_RMD_F4,A,B,C,D,E,15,8,J0) L(VG_RMD_F4,E,A,B,C,D,8,11,J0)
     L(VG_RMD_F4,D,E,A,B,C,1,14,J0) L(VG_RMD_F4,C,D,E,A,B,10,14,J0) L(VG_RMD_F4,B,C,D,E,A,3,12,J0) L(VG_RMD_F4,A,B,C,D,E,12,6,J0)
+    hk.at(13);
 #define J1 0x5C4DD124u
     L(VG_RMD_F3,E,A,B,C,D,6,9,J1) L(VG_RMD_F3,D,E,A,B,C,11,13,J1) L(VG_RMD_F3,C,D,E,A,B,3,15,J1) L(VG_RMD_F3,B,C,D,E,A,7,7,J1)
     L(VG_RMD_F3,A,B,C,D,E,0,12,J1) L(VG_RMD_F3,E,A,B,C,D,13,8,J1) L(VG_RMD_F3,D,E,A,B,C,5,9,J1) L(VG_RMD_F3,C,D,E,A,B,10,11,J1)
     L(VG_RMD_F3,B,C,D,E,A,14,7,J1) L(VG_RMD_F3,A,B,C,D,E,15,7,J1) L(VG_RMD_F3,E,A,B,C,D,8,12,J1) L(VG_RMD_F3,D,E,A,B,C,12,7,J1)
     L(VG_RMD_F3,C,D,E,A,B,4,6,J1) L(VG_RMD_F3,B,C,D,E,A,9,15,J1) L(VG_RMD_F3,A,B,C,D,E,1,13,J1) L(VG_RMD_F3,E,A,B,C,D,2,11,J1)
+    hk.at(14);
 #define J2 0x6D703EF3u
     L(VG_RMD_F2,D,E,A,B,C,15,9,J2) L(VG_RMD_F2,C,D,E,A,B,5,7,J2) L(VG_RMD_F2,B,C,D,E,A,1,15,J2) L(VG_RMD_F2,A,B,C,D,E,3,11,J2)
     L(VG_RMD_F2,E,A,B,C,D,7,8,J2) L(VG_RMD_F2,D,E,A,B,C,14,6,J2) L(VG_RMD_F2,C,D,E,A,B,6,6,J2) L(VG_RMD_F2,B,C,D,E,A,9,14,J2)
     L(VG_RMD_F2,A,B,C,D,E,11,12,J2) L(VG_RMD_F2,E,A,B,C,D,8,13,J2) L(VG_RMD_F2,D,E,A,B,C,12,5,J2) L(VG_RMD_F2,C,D,E,A,B,2,14,J2)
     L(VG_RMD_F2,B,C,D,E,A,10,13,J2) L(VG_RMD_F2,A,B,C,D,E,0,13,J2) L(VG_RMD_F2,E,A,B,C,D,4,7,J2) L(VG_RMD_F2,D,E,A,B,C,13,5,J2)
+    hk.at(15);
 #define J3 0x7A6D76E9u
     L(VG_RMD_F1,C,D,E,A,B,8,15,J3) L(VG_RMD_F1,B,C,D,E,A,6,5,J3) L(VG_RMD_F1,A,B,C,D,E,4,8,J3) L(VG_RMD_F1,E,A,B,C,D,1,11,J3)
     L(VG_RMD_F1,D,E,A,B,C,3,14,J3) L(VG_RMD_F1,C,D,E,A,B,11,14,J3) L(VG_RMD_F1,B,C,D,E,A,15,6,J3) L(VG_RMD_F1,A,B,C,D,E,0,14,J3)
     L(VG_RMD_F1,E,A,B,C,D,5,6,J3) L(VG_RMD_F1,D,E,A,B,C,12,9,J3) L(VG_RMD_F1,C,D,E,A,B,2,12,J3) L(VG_RMD_F1,B,C,D,E,A,13,9,J3)
     L(VG_RMD_F1,A,B,C,D,E,9,12,J3) L(VG_RMD_F1,E,A,B,C,D,7,5,J3) L(VG_RMD_F1,D,E,A,B,C,10,15,J3) L(VG_RMD_F1,C,D,E,A,B,14,8,J3)
+    hk.at(16);
     L(VG_RMD_F0,B,C,D,E,A,12,8,0u) L(VG_RMD_F0,A,B,C,D,E,15,5,0u) L(VG_RMD_F0,E,A,B,C,D,10,12,0u) L(VG_RMD_F0,D,E,A,B,C,4,9,0u)
     L(VG_RMD_F0,C,D,E,A,B,1,12,0u) L(VG_RMD_F0,B,C,D,E,A,5,5,0u) L(VG_RMD_F0,A,B,C,D,E,8,14,0u) L(VG_RMD_F0,E,A,B,C,D,7,6,0u)
     L(VG_RMD_F0,D,E,A,B,C,6,8,0u) L(VG_RMD_F0,C,D,E,A,B,2,13,0u) L(VG_RMD_F0,B,C,D,E,A,13,6,0u) L(VG_RMD_F0,A,B,C,D,E,14,5,0u)
     L(VG_RMD_F0,E,A,B,C,D,0,15,0u) L(VG_RMD_F0,D,E,A,B,C,3,13,0u) L(VG_RMD_F0,C,D,E,A,B,9,11,0u) L(VG_RMD_F0,B,C,D,E,A,11,11,0u)
 #undef L
+    hk.at(17);
     out[0] = c + D + h1; out[1] = d + E + h2; out[2] = e + A + h3; out[3] = a + B + h4; out[4] = b + C + h0;
 }
-// hash160 words (little-endian: digest byte 4i+j = byte j of out[i])
 template <class T>
-VG_DEV void hash160_pub33(T out[5], const T &prefix, const T xv[8]) {
-    T s[8]; sha256_pub33(s, prefix, xv); ripemd160_32(out, s);
+VG_DEV void ripemd160_32(T out[5], const T sha[8]) { vg_no_hook nh; ripemd160_32<T, vg_no_hook>(out, sha, nh); }
+// hash160 words (little-endian: digest byte 4i+j = byte j of out[i])
+template <class T, class Hook>
+VG_DEV void hash160_pub33(T out[5], const T &prefix, const T xv[8], Hook &hk) {
+    T s[8]; sha256_pub33<T, Hook>(s, prefix, xv, hk); ripemd160_32<T, Hook>(out, s, hk);
 }
+template <class T>
+VG_DEV void hash160_pub33(T out[5], const T &prefix, const T xv[8]) { vg_no_hook nh; hash160_pub33<T, vg_no_hook>(out, prefix, xv, nh); }
 template <class T>
 VG_DEV void hash160_pub65(T out[5], const T xv[8], const T yv[8]) {
     T s[8]; sha256_pub65(s, xv, yv); ripemd160_32(out, s);

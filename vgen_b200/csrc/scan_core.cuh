@@ -187,6 +187,48 @@ VG_DEV void vg_process_pair(const vg_scan_params &P, const vg_dfa_view &dv, fe &
 #define VG_LOAD_FE(dst, base, stride_words) { VG_UNROLL for (int _l = 0; _l < 8; _l++) (dst).v[_l] = (base)[(size_t)_l * (stride_words)]; }
 #define VG_STORE_FE(base, stride_words, src) { VG_UNROLL for (int _l = 0; _l < 8; _l++) (base)[(size_t)_l * (stride_words)] = (src).v[_l]; }
 
+// VG_PIPELINE = 1 (hash160-of-compressed-key formats only): software pipelining inside a thread. While a point is being hashed
+// (2,300 ALU-pipe instructions in a row) the field multiplications that produce the NEXT point (multiplier-pipe work) are issued
+// between the hash rounds through the hook points of hash.cuh, so that a warp feeds both integer pipes at once instead of
+// alternating between a multiplier-bound EC stretch and an ALU-bound hash stretch. Same results, different instruction order.
+#ifndef VG_PIPELINE
+#define VG_PIPELINE 0
+#endif
+#if VG_PIPELINE && !defined(VG_HOST_EMU)
+// The next point of the walk, computed in stages at the hook points of the hash of the current one. One struct for both kinds of
+// step, so that the loop body holds ONE copy of the hash (two copies, one per kind, doubled the code: 5,660 against 6,236 Mkeys/s,
+// "no instruction" stall 1.28 per issue, profiles/ncu_walk_pipe_r02_summary.txt):
+//   peel = false: (cx, cy) - i*G with the inverse inv_i already peeled for step i;
+//   peel = true : peel the inverse of the next step (inv_i = inv * pre, inv *= dx), then (cx, cy) + i*G.
+struct vg_stage_next {
+    const fe &cx, &cy; const uint32_t *g; const uint32_t *pre_ptr; size_t stride; fe &inv, &inv_i; bool peel, active;
+    fe lam, x3, y3;
+    VG_DEVM void at(int k) {
+        if (!active) return;
+        if (k == 0) {
+            if (peel) { fe pre; VG_LOAD_FE(pre, pre_ptr, stride); fe_mul(inv_i, inv, pre); }
+        } else if (k == 2) {
+            if (peel) {
+                fe gx, dx; VG_UNROLL for (int l = 0; l < 8; l++) gx.v[l] = g[l];
+                fe_sub(dx, gx, cx);
+                if (fe_is_zero_raw(dx)) fe_set_one(dx);
+                fe_mul(inv, inv, dx);
+            }
+        } else if (k == 4) {
+            fe gy, dy; VG_UNROLL for (int l = 0; l < 8; l++) gy.v[l] = g[8 + l];
+            if (!peel) fe_neg(gy, gy);
+            fe_sub(dy, gy, cy);
+            fe_mul(lam, dy, inv_i);
+        } else if (k == 6) {
+            fe gx; VG_UNROLL for (int l = 0; l < 8; l++) gx.v[l] = g[l];
+            fe_sqr(x3, lam); fe_sub(x3, x3, cx); fe_sub(x3, x3, gx);
+        } else if (k == 10) {
+            fe t; fe_sub(t, cx, x3); fe_mul(y3, lam, t); fe_sub(y3, y3, cy);
+        } else if (k == 14) { fe_canon(x3); fe_canon(y3); }
+    }
+};
+#endif
+
 // gtab: pointer to the i*G table (shared memory in the kernel), entry i-1 = 16 words
 template <int FMT, int MODE>
 VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const uint32_t *gtab, uint32_t tid) {
@@ -218,6 +260,42 @@ VG_DEV void vg_walk_thread(const vg_scan_params &P, const vg_dfa_view &dv, const
     const unsigned long long idx_c = (unsigned long long)tid * (2ull * H) + H;
 #if VG_SYNC_ITER && VG_PHASE_SPLIT && !defined(VG_HOST_EMU)
     const bool late_half = threadIdx.x >= blockDim.x / 2;
+#endif
+#if VG_PIPELINE && !defined(VG_HOST_EMU)
+    if (FMT == VG_FMT_P2PKH || FMT == VG_FMT_P2WPKH) {
+        // prologue: peel step H; the first point of the walk is the centre itself (it stands in for +H, which belongs to the next
+        // thread's batch)
+        fe inv_i, xa = cx, ya = cy;
+        unsigned long long idx_a = idx_c;
+        {
+            const uint32_t *g = gtab + (size_t)(H - 1) * 16;
+            fe gx, pre; VG_UNROLL for (int l = 0; l < 8; l++) gx.v[l] = g[l];
+            VG_LOAD_FE(pre, scr + (size_t)(H - 1) * 8 * T, T);
+            fe_mul(inv_i, inv, pre);
+            fe_sub(dx, gx, cx);
+            if (fe_is_zero_raw(dx)) fe_set_one(dx);
+            fe_mul(inv, inv, dx);
+        }
+        // slot 2(H - i) hashes (i, +) [the centre for i = H] while (i, -) is computed; slot 2(H - i) + 1 hashes (i, -) while the inverse
+        // of step i - 1 is peeled and (i - 1, +) is computed
+        #pragma unroll 1
+        for (uint32_t slot = 0; slot < 2 * H; slot++) {
+            const uint32_t i = H - (slot >> 1);
+            const bool second = (slot & 1u) != 0;
+  #if VG_SYNC_ITER
+            if (!second && (i % VG_SYNC_ITER) == 0) __syncthreads();
+  #endif
+            const uint32_t j = second ? i - 1 : i;              // step of the NEXT point
+            const bool active = j >= 1;
+            const uint32_t jj = active ? j : 1;
+            vg_stage_next nx{cx, cy, gtab + (size_t)(jj - 1) * 16, scr + (size_t)(jj - 1) * 8 * T, (size_t)T, inv, inv_i, second, active};
+            uint32_t dg[VG_DIGEST_WORDS];
+            VG_UNROLL for (int w = 5; w < VG_DIGEST_WORDS; w++) dg[w] = 0;
+            hash160_pub33<uint32_t, vg_stage_next>(dg, (ya.v[0] & 1u) + 2u, xa.v, nx);
+            vg_finish_point<FMT, MODE>(P, dv, dg, idx_a, !degenerate);
+            if (active) { xa = nx.x3; ya = nx.y3; idx_a = second ? idx_c + j : idx_c - j; }
+        }
+    } else
 #endif
     // backward pass: peel one inverse per step, derive both neighbours, hash, match
     for (uint32_t i = H; i >= 1; i--) {
