@@ -108,6 +108,26 @@ int vgen_cuda_digest_batch(vgen_ctx *ctx, int format, const uint8_t start_be[32]
  * key — what the reference's dispatch_p2tr / await_result_p2tr return (src/gpu.rs:667-807) */
 #define VGEN_P2TR_INTERNAL_KEY 6
 
+/* hash160 batch WITHOUT any allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as vgen_cuda_hash160_batch (hash160 of the compressed public key of n sequential scalars from start_be, 20 bytes
+ * each, zeros for scalars 0 and >= the group order) and the same kernels, but it needs no context and everything the kernels
+ * work in lives in one file-scope __device__ array of the library (vgen_b200/csrc/static_batch.cu: 17.45 MB, present on every
+ * GPU that loads the library until the process exits) instead of cudaMalloc'ed buffers. The call never calls cudaMalloc,
+ * cudaFree, cudaHostAlloc or an allocating library routine.
+ *   device      CUDA device ordinal (made current by the call)
+ *   n           at most VGEN_STATIC_MAX_KEYS; more is rejected with VGEN_ERR_INVALID_ARG and a message, nothing is launched
+ *   out20_dev   caller-owned DEVICE memory, n * 20 bytes
+ *   cuda_stream cudaStream_t the work is queued on (NULL: the default stream). The call returns once the work is queued; it
+ *               synchronises the stream only on the first call per device (table set-up), which therefore must not be made
+ *               under graph capture
+ *   err         message buffer (may be NULL)
+ * All calls on one device share the array, which keeps the last call's contents (the call clears what must start at zero):
+ * calls that overlap on the GPU — different streams without an event between them — race. Serialise them. */
+#define VGEN_STATIC_MAX_KEYS (1u << 20)
+int vgen_cuda_hash160_batch_static(int device, const uint8_t start_be[32], uint32_t n, uint8_t *out20_dev, void *cuda_stream,
+                                   char *err, size_t err_cap);
+
 /* Device-resident timing for bench.py: centres set up untimed, then n_windows full-size windows of the current
  * pattern timed with CUDA events on lane 0's stream. */
 int vgen_cuda_bench_resident(vgen_ctx *ctx, const uint8_t start_be[32], uint32_t n_windows, float *ms, uint64_t *keys, uint64_t *launches);

@@ -83,6 +83,11 @@ extern "C" {
     fn vgen_cuda_scan_total_hits(ctx: *const VgenCtx) -> u64;
     fn vgen_cuda_scan_fetch_hits(ctx: *const VgenCtx, offset: u64, out: *mut VgenHit, cap: u64) -> u64;
     fn vgen_cuda_hash160_batch(ctx: *mut VgenCtx, start_be: *const u8, n: u64, out20: *mut u8) -> c_int;
+    /// Allocation-free variant (static device work area, at most 2^20 keys per call, `out20_dev` is DEVICE memory). Not used by
+    /// `GpuRunner`: it exists for callers under CUDA graph capture. See include/vgen_cuda.h.
+    #[allow(dead_code)]
+    fn vgen_cuda_hash160_batch_static(device: c_int, start_be: *const u8, n: u32, out20_dev: *mut u8, cuda_stream: *mut c_void,
+                                      err: *mut c_char, err_cap: usize) -> c_int;
     fn vgen_cuda_digest_batch(ctx: *mut VgenCtx, format: c_int, start_be: *const u8, n: u64, out: *mut u8, stride: u32) -> c_int;
     fn vgen_cuda_window_keys(ctx: *const VgenCtx) -> u64;
     fn vgen_format_address(format: c_int, digest: *const u8, out: *mut c_char, cap: usize) -> c_int;

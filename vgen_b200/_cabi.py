@@ -38,6 +38,8 @@ SYMBOLS = {
     "vgen_cuda_scan_text": (C.c_int, [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_uint64)]),
     "vgen_cuda_hash160_batch": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint64, C.c_void_p]),
     "vgen_cuda_digest_batch": (C.c_int, [C.c_void_p, C.c_int, C.c_char_p, C.c_uint64, C.c_void_p, C.c_uint32]),
+    # allocation-free hash160 batch (static device work area; out is a DEVICE pointer): device, start, n, out20_dev, stream, err, err_cap
+    "vgen_cuda_hash160_batch_static": (C.c_int, [C.c_int, C.c_char_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t]),
     "vgen_cuda_bench_resident": (C.c_int, [C.c_void_p, C.c_char_p, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
     "vgen_cuda_launch_count": (C.c_uint64, [C.c_void_p]),
     "vgen_cuda_window_keys": (C.c_uint64, [C.c_void_p]),
