@@ -62,11 +62,30 @@ def main():
         assert len(r.digest_batch(fmt, S + 7, 1025)) == 1025 * (32 if fmt == "p2tr" else 20)
     r.dispatch_p2tr(S, 0, n=777)
     assert len(r.await_result_p2tr(0)[0]) == 777
+    static_batch(r)
     st = r.stats()
     print("stats", st, flush=True)
     assert st["damaged_guards"] == 0, st
     r.close()
     print("SANITIZE_DRIVER_OK")
+
+
+def static_batch(r):
+    """the allocation-free entry point (static_batch.cu): same kernels, work area in a __device__ array; output into torch memory"""
+    import ctypes as C
+    import torch
+    from vgen_b200 import _cabi
+    L = _cabi.lib()
+    err = C.create_string_buffer(256)
+    for start, n in [(0, 5000), (N - 3000, 5000), (S + 99, 1 << 20), (S, 1)]:
+        out = torch.full((n * 20,), 0xEE, dtype=torch.uint8, device="cuda:0")
+        assert L.vgen_cuda_hash160_batch_static(0, start.to_bytes(32, "big"), n, out.data_ptr(), None, err, len(err)) == 0, err.value
+        got = out.cpu().numpy().tobytes()
+        assert got == b"".join(r.generate_batch(start, n)), (hex(start), n)
+        viol = (C.c_uint32 * 2)(0, 0)
+        if hasattr(L, "vgen_cuda_static_violations"):           # checked build only
+            assert L.vgen_cuda_static_violations(0, viol) == 0 and list(viol) == [0, 0], list(viol)
+        print("%-20s %-28s %-10s keys %8d violations %s" % ("static hash160", hex(start)[:28], "dump", n, list(viol)), flush=True)
 
 
 if __name__ == "__main__":

@@ -149,3 +149,16 @@ extern "C" int vgen_cuda_hash160_batch_static(int device, const uint8_t start_be
     SB_CK(vg::launch_slow(VG_FMT_P2PKH, VG_MODE_DUMP, P, base + kOffScalars + 8, base + kOffGtable, 0xffffffffu, s));
     return VGEN_OK;
 }
+
+#ifdef VG_CHECKED
+// checked build only (tools/sanitize.sh): the device-side bounds checks of the last call on `device`: out[0] = code of the first
+// failed check (scan_core.cuh), out[1] = how many failed. Synchronises the device.
+extern "C" int vgen_cuda_static_violations(int device, uint32_t out[2]) {
+    if (device < 0 || device >= kMaxDevices || !out) return VGEN_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> g(g_state_mu);
+    if (!g_state[device].ready) { out[0] = out[1] = 0; return VGEN_OK; }
+    if (cudaSetDevice(device) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess ||
+        cudaMemcpy(out, g_state[device].base + kOffCounters + 2, 8, cudaMemcpyDeviceToHost) != cudaSuccess) return VGEN_ERR_CUDA;
+    return VGEN_OK;
+}
+#endif
