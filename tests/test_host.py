@@ -319,6 +319,26 @@ def test_published_vectors_through_the_product_encoders(published):
     assert vg.Pattern("^" + e.lower() + "$").lowering(F.Ethereum)["kind"] == "none"      # wrong case can never match the EIP-55 form
 
 
+def test_product_encoders_vs_oracle_random_and_leading_zeros():
+    """vgen_format_address / vgen_format_wif (host_util.cpp: SHA-256, Keccak, Base58 on 32-bit limbs in groups of five digits,
+    Bech32(m)) against the oracle's independent encoders: random digests and keys, runs of leading zero bytes (Base58 '1's, a top
+    digit group without leading zeros), all-zero and all-ones inputs."""
+    import random
+    rnd = random.Random(58)
+    F = vg.AddressFormat
+    cases = [bytes(32), b"\xff" * 32, b"\0" * 19 + b"\1" + bytes(12), b"\0" * 31 + b"\1"]
+    cases += [b"\0" * k + bytes(rnd.randrange(1, 256) for _ in range(32 - k)) for k in range(0, 32)]
+    cases += [bytes(rnd.randrange(256) for _ in range(32)) for _ in range(1500)]
+    for d in cases:
+        for fmt in (F.P2pkh, F.P2pkhUncompressed, F.P2wpkh, F.P2shP2wpkh, F.P2tr, F.Ethereum):
+            n = 32 if fmt == F.P2tr else 20
+            assert vg.address_from_digest(fmt, d[:n]) == oracle.address_from_digest(int(fmt), d[:n]), (fmt, d.hex())
+        # WIF = Base58Check(0x80 || key [|| 0x01]) for any 32 bytes (the encoder does not look at the scalar's range)
+        assert vg.wif_from_key(F.P2pkh, d) == oracle.base58check(b"\x80" + d + b"\x01")
+        assert vg.wif_from_key(F.P2pkhUncompressed, d) == oracle.base58check(b"\x80" + d)
+        assert vg.wif_from_key(F.Ethereum, d) == d.hex()
+
+
 def test_regex_too_big_for_a_device_table_falls_back_to_the_host_nfa(regex_golden):
     """A pattern vgen accepts must not become an error after the swap (src/pattern.rs:21-40 takes whatever `regex` compiles).
     `a.{13}$` needs 2^14 DFA states, more than a device table holds: Pattern still compiles, matches() decides with the NFA, and

@@ -23,79 +23,123 @@ const uint32_t K256[64] = {
     0x650a7354,0x766a0abb,0x81c2c92e,0x92722c85,0xa2bfe8a1,0xa81a664b,0xc24b8b70,0xc76c51a3,0xd192e819,0xd6990624,0xf40e3585,0x106aa070,
     0x19a4c116,0x1e376c08,0x2748774c,0x34b0bcb5,0x391c0cb3,0x4ed8aa4a,0x5b9cca4f,0x682e6ff3,0x748f82ee,0x78a5636f,0x84c87814,0x8cc70208,
     0x90befffa,0xa4506ceb,0xbef9a3f7,0xc67178f2};
+// one compression; rolling 16-word schedule, state rotated by renaming (the confirm workers hash four blocks per hit)
+#define VG_S0(x) (ror(x, 2) ^ ror(x, 13) ^ ror(x, 22))
+#define VG_S1(x) (ror(x, 6) ^ ror(x, 11) ^ ror(x, 25))
+#define VG_s0(x) (ror(x, 7) ^ ror(x, 18) ^ ((x) >> 3))
+#define VG_s1(x) (ror(x, 17) ^ ror(x, 19) ^ ((x) >> 10))
+#define VG_RND(a, b, c, d, e, f, g, h, i) { \
+    uint32_t t1 = h + VG_S1(e) + ((e & f) ^ (~e & g)) + K256[i] + w[(i) & 15]; \
+    uint32_t t2 = VG_S0(a) + ((a & b) | (c & (a | b))); \
+    d += t1; h = t1 + t2; }
+#define VG_SCHED(i) w[(i) & 15] += VG_s0(w[((i) + 1) & 15]) + w[((i) + 9) & 15] + VG_s1(w[((i) + 14) & 15])
 void sha_block(uint32_t s[8], const uint8_t *p) {
-    uint32_t w[64];
+    uint32_t w[16];
     for (int i = 0; i < 16; i++) w[i] = (uint32_t)p[4 * i] << 24 | (uint32_t)p[4 * i + 1] << 16 | (uint32_t)p[4 * i + 2] << 8 | p[4 * i + 3];
-    for (int i = 16; i < 64; i++)
-        w[i] = w[i - 16] + (ror(w[i - 15], 7) ^ ror(w[i - 15], 18) ^ (w[i - 15] >> 3)) + w[i - 7] + (ror(w[i - 2], 17) ^ ror(w[i - 2], 19) ^ (w[i - 2] >> 10));
-    uint32_t v[8]; memcpy(v, s, 32);
-    for (int i = 0; i < 64; i++) {
-        uint32_t t1 = v[7] + (ror(v[4], 6) ^ ror(v[4], 11) ^ ror(v[4], 25)) + ((v[4] & v[5]) ^ (~v[4] & v[6])) + K256[i] + w[i];
-        uint32_t t2 = (ror(v[0], 2) ^ ror(v[0], 13) ^ ror(v[0], 22)) + ((v[0] & v[1]) ^ (v[0] & v[2]) ^ (v[1] & v[2]));
-        for (int j = 7; j > 0; j--) v[j] = v[j - 1];
-        v[4] += t1; v[0] = t1 + t2;
+    uint32_t a = s[0], b = s[1], c = s[2], d = s[3], e = s[4], f = s[5], g = s[6], h = s[7];
+#pragma GCC unroll 8
+    for (int i = 0; i < 64; i += 8) {
+        if (i >= 16) { VG_SCHED(i); VG_SCHED(i + 1); VG_SCHED(i + 2); VG_SCHED(i + 3); VG_SCHED(i + 4); VG_SCHED(i + 5); VG_SCHED(i + 6); VG_SCHED(i + 7); }
+        VG_RND(a, b, c, d, e, f, g, h, i);     VG_RND(h, a, b, c, d, e, f, g, i + 1); VG_RND(g, h, a, b, c, d, e, f, i + 2); VG_RND(f, g, h, a, b, c, d, e, i + 3);
+        VG_RND(e, f, g, h, a, b, c, d, i + 4); VG_RND(d, e, f, g, h, a, b, c, i + 5); VG_RND(c, d, e, f, g, h, a, b, i + 6); VG_RND(b, c, d, e, f, g, h, a, i + 7);
     }
-    for (int i = 0; i < 8; i++) s[i] += v[i];
+    s[0] += a; s[1] += b; s[2] += c; s[3] += d; s[4] += e; s[5] += f; s[6] += g; s[7] += h;
 }
+#undef VG_S0
+#undef VG_S1
+#undef VG_s0
+#undef VG_s1
+#undef VG_RND
+#undef VG_SCHED
 }  // namespace
 
 void h_sha256(const uint8_t *msg, size_t len, uint8_t out[32]) {
     uint32_t s[8] = {0x6a09e667,0xbb67ae85,0x3c6ef372,0xa54ff53a,0x510e527f,0x9b05688c,0x1f83d9ab,0x5be0cd19};
-    std::vector<uint8_t> m(msg, msg + len);
-    m.push_back(0x80);
-    while (m.size() % 64 != 56) m.push_back(0);
-    uint64_t bits = (uint64_t)len * 8;
-    for (int i = 7; i >= 0; i--) m.push_back((uint8_t)(bits >> (8 * i)));
-    for (size_t o = 0; o < m.size(); o += 64) sha_block(s, m.data() + o);
+    size_t o = 0;
+    for (; o + 64 <= len; o += 64) sha_block(s, msg + o);
+    uint8_t blk[64];
+    size_t r = len - o;
+    memcpy(blk, msg + o, r);
+    blk[r++] = 0x80;
+    if (r > 56) { memset(blk + r, 0, 64 - r); sha_block(s, blk); r = 0; }
+    memset(blk + r, 0, 56 - r);
+    const uint64_t bits = (uint64_t)len * 8;
+    for (int i = 0; i < 8; i++) blk[56 + i] = (uint8_t)(bits >> (8 * (7 - i)));
+    sha_block(s, blk);
     for (int i = 0; i < 8; i++) { out[4 * i] = s[i] >> 24; out[4 * i + 1] = s[i] >> 16; out[4 * i + 2] = s[i] >> 8; out[4 * i + 3] = s[i]; }
 }
 
-void h_keccak256(const uint8_t *msg, size_t len, uint8_t out[32]) {
+namespace {
+// Keccak-f[1600] on 25 lanes, lane (x, y) at index x + 5y
+void keccak_f(uint64_t st[25]) {
     static const uint64_t RC[24] = {
         0x0000000000000001ULL,0x0000000000008082ULL,0x800000000000808aULL,0x8000000080008000ULL,0x000000000000808bULL,0x0000000080000001ULL,
         0x8000000080008081ULL,0x8000000000008009ULL,0x000000000000008aULL,0x0000000000000088ULL,0x0000000080008009ULL,0x000000008000000aULL,
         0x000000008000808bULL,0x800000000000008bULL,0x8000000000008089ULL,0x8000000000008003ULL,0x8000000000008002ULL,0x8000000000000080ULL,
         0x000000000000800aULL,0x800000008000000aULL,0x8000000080008081ULL,0x8000000000008080ULL,0x0000000080000001ULL,0x8000000080008008ULL};
-    uint64_t a[5][5] = {};   // a[x][y]
-    const size_t rate = 136;
-    std::vector<uint8_t> m(msg, msg + len);
-    size_t pad = rate - m.size() % rate;
-    m.resize(m.size() + pad, 0);
-    m[len] ^= 0x01; m[m.size() - 1] ^= 0x80;
-    auto rol = [](uint64_t v, unsigned n) { return n ? (v << n) | (v >> (64 - n)) : v; };
-    for (size_t o = 0; o < m.size(); o += rate) {
-        for (size_t i = 0; i < rate / 8; i++) { uint64_t v = 0; for (int b = 7; b >= 0; b--) v = (v << 8) | m[o + 8 * i + b]; a[i % 5][i / 5] ^= v; }
-        for (int r = 0; r < 24; r++) {
-            uint64_t c[5], d[5], b[5][5];
-            for (int x = 0; x < 5; x++) c[x] = a[x][0] ^ a[x][1] ^ a[x][2] ^ a[x][3] ^ a[x][4];
-            for (int x = 0; x < 5; x++) d[x] = c[(x + 4) % 5] ^ rol(c[(x + 1) % 5], 1);
-            for (int x = 0; x < 5; x++) for (int y = 0; y < 5; y++) a[x][y] ^= d[x];
-            // rho + pi: walk the (x, y) -> (y, 2x+3y) orbit with triangular-number rotations
-            b[0][0] = a[0][0];
-            int x = 1, y = 0;
-            for (int t = 0; t < 24; t++) {
-                unsigned rot = ((t + 1) * (t + 2) / 2) % 64;
-                b[y][(2 * x + 3 * y) % 5] = rol(a[x][y], rot);
-                int nx = y, ny = (2 * x + 3 * y) % 5; x = nx; y = ny;
-            }
-            for (int xx = 0; xx < 5; xx++) for (int yy = 0; yy < 5; yy++) a[xx][yy] = b[xx][yy] ^ (~b[(xx + 1) % 5][yy] & b[(xx + 2) % 5][yy]);
-            a[0][0] ^= RC[r];
+    // rho rotation of the t-th lane on the pi orbit that starts at (1, 0), and where that lane goes
+    static constexpr int ROT[24] = {1, 3, 6, 10, 15, 21, 28, 36, 45, 55, 2, 14, 27, 41, 56, 8, 25, 43, 62, 18, 39, 61, 20, 44};
+    static constexpr int DST[24] = {10, 7, 11, 17, 18, 3, 5, 16, 8, 21, 24, 4, 15, 23, 19, 13, 12, 2, 20, 14, 22, 9, 6, 1};
+    for (int r = 0; r < 24; r++) {
+        uint64_t c[5];
+#pragma GCC unroll 5
+        for (int x = 0; x < 5; x++) c[x] = st[x] ^ st[x + 5] ^ st[x + 10] ^ st[x + 15] ^ st[x + 20];
+#pragma GCC unroll 5
+        for (int x = 0; x < 5; x++) {
+            const uint64_t n = c[(x + 1) % 5], d = c[(x + 4) % 5] ^ ((n << 1) | (n >> 63));
+            st[x] ^= d; st[x + 5] ^= d; st[x + 10] ^= d; st[x + 15] ^= d; st[x + 20] ^= d;
         }
+        uint64_t t = st[1];
+#pragma GCC unroll 24
+        for (int i = 0; i < 24; i++) { const int j = DST[i]; const uint64_t keep = st[j]; st[j] = (t << ROT[i]) | (t >> (64 - ROT[i])); t = keep; }
+#pragma GCC unroll 5
+        for (int y = 0; y < 25; y += 5) {
+            const uint64_t r0 = st[y], r1 = st[y + 1], r2 = st[y + 2], r3 = st[y + 3], r4 = st[y + 4];
+            st[y] = r0 ^ (~r1 & r2); st[y + 1] = r1 ^ (~r2 & r3); st[y + 2] = r2 ^ (~r3 & r4); st[y + 3] = r3 ^ (~r4 & r0); st[y + 4] = r4 ^ (~r0 & r1);
+        }
+        st[0] ^= RC[r];
     }
-    for (int i = 0; i < 4; i++) for (int b = 0; b < 8; b++) out[8 * i + b] = (uint8_t)(a[i % 5][i / 5] >> (8 * b));
+}
+}  // namespace
+
+void h_keccak256(const uint8_t *msg, size_t len, uint8_t out[32]) {
+    const size_t rate = 136;
+    uint64_t st[25] = {};
+    auto absorb = [&](const uint8_t *blk) {
+        for (size_t i = 0; i < rate / 8; i++) { uint64_t v = 0; for (int b = 7; b >= 0; b--) v = (v << 8) | blk[8 * i + b]; st[i] ^= v; }
+        keccak_f(st);
+    };
+    size_t o = 0;
+    for (; o + rate <= len; o += rate) absorb(msg + o);
+    uint8_t blk[136];
+    memset(blk, 0, sizeof blk);
+    memcpy(blk, msg + o, len - o);
+    blk[len - o] ^= 0x01; blk[rate - 1] ^= 0x80;       // original Keccak padding (not SHA-3's 0x06)
+    absorb(blk);
+    for (int i = 0; i < 4; i++) for (int b = 0; b < 8; b++) out[8 * i + b] = (uint8_t)(st[i] >> (8 * b));
 }
 
+// Base58 of a big-endian byte string. The number is divided by 58^5 on 32-bit limbs (one 64-by-32 division per limb and
+// five digits per pass) instead of by 58 on bytes: ~100 divisions for a 25-byte address payload instead of ~850.
 std::string h_base58(const uint8_t *data, size_t len) {
     size_t zeros = 0;
     while (zeros < len && data[zeros] == 0) zeros++;
-    std::vector<uint8_t> num(data + zeros, data + len);   // big-endian base-256
-    std::string digits;
-    size_t start = 0;
-    while (start < num.size()) {
-        unsigned rem = 0;
-        for (size_t i = start; i < num.size(); i++) { unsigned cur = rem * 256 + num[i]; num[i] = (uint8_t)(cur / 58); rem = cur % 58; }
-        digits.push_back(B58_ALPHABET[rem]);
-        while (start < num.size() && num[start] == 0) start++;
+    const size_t nb = len - zeros;
+    std::vector<uint32_t> limb((nb + 3) / 4, 0);      // most significant limb first
+    for (size_t i = 0; i < nb; i++) {
+        const size_t from_end = nb - 1 - i;            // byte significance
+        limb[limb.size() - 1 - from_end / 4] |= (uint32_t)data[zeros + i] << (8 * (from_end % 4));
+    }
+    std::string digits;                                // least significant first
+    digits.reserve(nb * 138 / 100 + 8);
+    size_t first = 0;
+    while (first < limb.size() && limb[first] == 0) first++;
+    while (first < limb.size()) {
+        uint64_t rem = 0;
+        for (size_t i = first; i < limb.size(); i++) { const uint64_t cur = (rem << 32) | limb[i]; limb[i] = (uint32_t)(cur / 656356768u); rem = cur % 656356768u; }
+        while (first < limb.size() && limb[first] == 0) first++;
+        const bool last = first == limb.size();        // the most significant group carries no leading zeros
+        for (int k = 0; k < 5 && (!last || rem); k++) { digits.push_back(B58_ALPHABET[rem % 58]); rem /= 58; }
     }
     std::string out(zeros, '1');
     out.append(digits.rbegin(), digits.rend());
@@ -104,6 +148,11 @@ std::string h_base58(const uint8_t *data, size_t len) {
 std::string h_base58check(const uint8_t *payload, size_t len) {
     uint8_t h1[32], h2[32];
     h_sha256(payload, len, h1); h_sha256(h1, 32, h2);
+    if (len <= 60) {
+        uint8_t buf[64];
+        memcpy(buf, payload, len); memcpy(buf + len, h2, 4);
+        return h_base58(buf, len + 4);
+    }
     std::vector<uint8_t> buf(payload, payload + len);
     buf.insert(buf.end(), h2, h2 + 4);
     return h_base58(buf.data(), buf.size());
@@ -133,7 +182,7 @@ namespace {
 uint32_t polymod_step(uint32_t c) {
     static const uint32_t G[5] = {0x3b6a57b2u, 0x26508e6du, 0x1ea119fau, 0x3d4233ddu, 0x2a1462b3u};
     uint32_t top = c >> 25; c = (c & 0x1ffffffu) << 5;
-    for (int i = 0; i < 5; i++) if ((top >> i) & 1) c ^= G[i];
+    for (int i = 0; i < 5; i++) c ^= (0u - ((top >> i) & 1u)) & G[i];
     return c;
 }
 uint32_t bech32_checksum_state(const std::vector<uint8_t> &data5) {
@@ -147,14 +196,24 @@ uint32_t bech32_checksum_state(const std::vector<uint8_t> &data5) {
 }
 }  // namespace
 std::string h_segwit(int witver, const uint8_t *prog, size_t len) {
-    std::vector<uint8_t> d5; d5.push_back((uint8_t)witver);
+    uint8_t d5[80]; size_t n = 0;                     // witness programs are at most 40 bytes: 1 + 64 groups + 6 checksum symbols
+    if (len > 40) len = 40;
+    d5[n++] = (uint8_t)witver;
     uint32_t acc = 0; int bits = 0;
-    for (size_t i = 0; i < len; i++) { acc = (acc << 8) | prog[i]; bits += 8; while (bits >= 5) { bits -= 5; d5.push_back((acc >> bits) & 31); } }
-    if (bits) d5.push_back((acc << (5 - bits)) & 31);
-    std::vector<uint8_t> ext = d5; ext.insert(ext.end(), 6, 0);
-    uint32_t pm = bech32_checksum_state(ext) ^ (witver == 0 ? 1u : 0x2bc830a3u);
-    std::string out = "bc1";
-    for (uint8_t d : d5) out.push_back(BECH32_ALPHABET[d]);
+    for (size_t i = 0; i < len; i++) { acc = (acc << 8) | prog[i]; bits += 8; while (bits >= 5) { bits -= 5; d5[n++] = (acc >> bits) & 31; } }
+    if (bits) d5[n++] = (acc << (5 - bits)) & 31;
+    uint32_t c = 1;
+    const char hrp[] = "bc";
+    for (int i = 0; i < 2; i++) c = polymod_step(c) ^ (uint32_t)(hrp[i] >> 5);
+    c = polymod_step(c);
+    for (int i = 0; i < 2; i++) c = polymod_step(c) ^ (uint32_t)(hrp[i] & 31);
+    for (size_t i = 0; i < n; i++) c = polymod_step(c) ^ d5[i];
+    for (int i = 0; i < 6; i++) c = polymod_step(c);
+    const uint32_t pm = c ^ (witver == 0 ? 1u : 0x2bc830a3u);
+    std::string out;
+    out.reserve(3 + n + 6);
+    out = "bc1";
+    for (size_t i = 0; i < n; i++) out.push_back(BECH32_ALPHABET[d5[i]]);
     for (int i = 0; i < 6; i++) out.push_back(BECH32_ALPHABET[(pm >> (5 * (5 - i))) & 31]);
     return out;
 }
