@@ -112,10 +112,12 @@ int emu_confirm_eth_fold(const uint32_t *dg, const uint16_t *table, const uint8_
     vg_dfa_view dv; dv.table = table; dv.accept = accept; dv.sym = sym_class;
     return vg_confirm<5>(m, dv, dg);
 }
-// P2TR stage 2 (taproot.cuh) over n keys (n a multiple of VG_TAP_GROUP) whose even-Y internal keys are in points[16*n]:
-// writes the 32-byte witness programs. bits = window width of the fixed-base table (4 keeps the host build cheap).
+// P2TR stage 2 (taproot.cuh) over n keys (n a multiple of VG_TAP_GROUP): key i has the scalar base8 + i and its public key (x, y) in
+// points[16*i ..] (all-zero = invalid), as stage 1 leaves them. Writes the 32-byte witness programs. bits = window width of the
+// fixed-base table (4 keeps the host build cheap).
 static std::vector<uint32_t> g_tap; static uint32_t g_tap_bits = 0;
-void emu_tap_stage2(uint32_t *points, uint32_t n, uint32_t bits, uint8_t *out32) {
+int emu_tap_scalar_form() { return VG_TAP_SCALAR; }
+void emu_tap_stage2(uint32_t *points, const uint32_t *base8, uint32_t n, uint32_t bits, uint8_t *out32) {
     ensure_pow2();
     if (g_tap_bits != bits) {
         const size_t cnt = (size_t)vg_tap_windows(bits) << bits;
@@ -131,6 +133,7 @@ void emu_tap_stage2(uint32_t *points, uint32_t n, uint32_t bits, uint8_t *out32)
     vg_scan_params P; memset(&P, 0, sizeof P);
     uint32_t hitc = 0;
     P.points = points; P.tap_table = g_tap.data(); P.tap_bits = bits; P.limit = n; P.dump = out32; P.dump_stride = 32; P.hit_count = &hitc;
+    memcpy(P.tap_base, base8, 32);
     vg_dfa_view dv; dv.table = nullptr; dv.accept = nullptr; dv.sym = nullptr;
     memset(out32, 0, (size_t)n * 32);
     for (uint32_t g = 0; g < n / VG_TAP_GROUP; g++) vg_tap_thread<VG_MODE_DUMP>(P, dv, (unsigned long long)g * VG_TAP_GROUP);
@@ -174,7 +177,10 @@ int emu_walk_dump(int fmt, const uint32_t *start, uint32_t T, uint32_t H, uint32
                 default: vg_walk_thread<5, VG_MODE_DUMP>(P, dv, gtab.data(), t); break;
             }
         }
-        if (fmt == 4) emu_tap_stage2(points.data(), (uint32_t)W, 4, P.dump);      // stride must be 32
+        if (fmt == 4) {
+            uint32_t wb[8]; scalar_add_u64(wb, start, (uint64_t)w * W);
+            emu_tap_stage2(points.data(), wb, (uint32_t)W, 4, P.dump);      // stride must be 32
+        }
     }
     return (int)degc;
 }

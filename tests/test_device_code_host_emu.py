@@ -137,24 +137,31 @@ def test_p2tr_two_stage_vs_oracle(emu):
 
 
 def test_p2tr_stage2_invalid_points_and_small_tweak_table(emu):
-    # all-zero points (invalid scalar / outside the range) give all-zero programs; 8-bit windows agree with 4-bit ones
-    ks = [1, 2, 3, 0, 2**200 + 9, N - 1, 0, 77, 5, 0, 0, 2**255, 12345, N - 2, 0, 9]
-    ks = ks + [0, 0, 3**150, 2**128 - 1] + list(range(100, 112)) + ks[::-1] + [7**80 + i for i in range(16)]   # 64: a multiple of VG_TAP_GROUP
-    pts = (C.c_uint32 * (16 * len(ks)))()
-    for i, k in enumerate(ks):
-        if k:
-            x, y = oracle.pubkey(k)
-            if y & 1:
-                y = P_FIELD - y
-            for l in range(8):
-                pts[16 * i + l] = (x >> (32 * l)) & 0xffffffff
-                pts[16 * i + 8 + l] = (y >> (32 * l)) & 0xffffffff
-    for bits in (4, 8, 5, 7):       # 5 and 7: digits straddle 32-bit limbs and the top window is partial (as with 24-bit windows)
-        out = C.create_string_buffer(32 * len(ks))
-        emu.emu_tap_stage2(pts, len(ks), bits, out)
+    """Stage 2 alone: 64 consecutive scalars from several bases, their public keys as stage 1 stores them (the scalar form reads
+    x, the parity of y and derives the key's scalar from the window base; the older form wants the even-Y point). All-zero points
+    (invalid scalar / outside the range) give all-zero programs; 8-, 5- and 7-bit windows agree with 4-bit ones."""
+    scalar_form = emu.emu_tap_scalar_form()
+    n = 64                                   # a multiple of VG_TAP_GROUP
+    for base, dropped in [(1, {3, 9, 10}), (2**200 + 9, set()), (N - 40, {0}), (2**255 - 17, {63}), (7**80, {5, 6, 7, 8})]:
+        ks = [base + i for i in range(n)]
+        pts = (C.c_uint32 * (16 * n))()
+        live = []
         for i, k in enumerate(ks):
-            want = oracle.digest_batch("p2tr", k, 1)[:32] if k else b"\0" * 32
-            assert out.raw[32 * i:32 * i + 32] == want, (bits, k)
+            if 0 < k < N and i not in dropped:
+                x, y = oracle.pubkey(k)
+                if not scalar_form and (y & 1):
+                    y = P_FIELD - y
+                for l in range(8):
+                    pts[16 * i + l] = (x >> (32 * l)) & 0xffffffff
+                    pts[16 * i + 8 + l] = (y >> (32 * l)) & 0xffffffff
+                live.append(i)
+        assert live
+        for bits in (4, 8, 5, 7):       # 5 and 7: digits straddle 32-bit limbs and the top window is partial (as with 24-bit windows)
+            out = C.create_string_buffer(32 * n)
+            emu.emu_tap_stage2(pts, limbs(base), n, bits, out)
+            for i, k in enumerate(ks):
+                want = oracle.digest_batch("p2tr", k, 1)[:32] if i in live else b"\0" * 32
+                assert out.raw[32 * i:32 * i + 32] == want, (bits, hex(k))
 
 
 @pytest.mark.parametrize("fmt,pats", [

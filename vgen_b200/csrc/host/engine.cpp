@@ -352,6 +352,7 @@ void Engine::fill_params(Lane &L, Slot &S, const uint32_t *stride16, vg_scan_par
     P.hits = S.d_hits; P.hit_count = S.d_counters; P.hit_cap = hit_cap_;
     P.degen_list = S.d_degen; P.degen_count = S.d_counters + 1; P.degen_cap = V.threads;
     P.points = L.d_points; P.tap_table = D.d_tap_table; P.tap_bits = tap_bits_;
+    S.task.base.to_limbs32(P.tap_base);
     P.violations = S.d_counters + 2;
     P.m = lp_.dev;
     P.m.dfa.table = D.d_dfa_table; P.m.dfa.accept = D.d_dfa_accept;
@@ -834,7 +835,12 @@ bool Engine::bench_resident(const U256 &start, uint32_t n_windows, float &ms, ui
         CK(cudaMemsetAsync(S.d_counters, 0, kCounterWords * 4, L.stream));
         CK(launch_walk(lp_.format, VG_MODE_MATCH, Ps[li], levels_[fl].blocks, L.stream));
         launches++;
-        if (lp_.format == VG_FMT_P2TR) { CK(launch_taptweak(VG_MODE_MATCH, Ps[li], L.stream)); launches++; }
+        if (lp_.format == VG_FMT_P2TR) {
+            // the lane's (w / lanes)-th window: its centres have moved on by that many strides of G lanes
+            const uint64_t G = (uint64_t)shard_count_ * nl;
+            S.task.base.add(U256(W).mul64(G).mul64(w / D.lanes.size())).to_limbs32(Ps[li].tap_base);
+            CK(launch_taptweak(VG_MODE_MATCH, Ps[li], L.stream)); launches++;
+        }
     }
     ms = 0;
     for (size_t d = 0; d < nd; d++) {

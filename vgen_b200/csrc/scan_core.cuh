@@ -25,6 +25,12 @@
 #endif
 #define VG_ASSERT(P, cond, code) VG_ASSERT_AT((P).violations, cond, code)
 
+// VG_TAP_SCALAR = 1 (P2TR): the output key is computed from the key's SCALAR, Q = (t + k) * G for even y(k*G) and (t + n - k) * G for
+// odd, entirely from the fixed-base table: one table addition fewer per key than P + t*G (the point P itself is only hashed).
+#ifndef VG_TAP_SCALAR
+#define VG_TAP_SCALAR 1
+#endif
+
 // digest words of N points at once (T = uint32_t or vw<N>); xv / yv = little-endian limbs of canonical coordinates
 template <int FMT, class T>
 VG_DEV void vg_digest_lanes(T dg[VG_DIGEST_WORDS], const T xv[8], const T yv[8]) {
@@ -132,13 +138,19 @@ template <int FMT, int MODE>
 VG_DEV void vg_process_point(const vg_scan_params &P, const vg_dfa_view &dv, fe &x, fe &y, unsigned long long idx, bool valid) {
     fe_canon(x); fe_canon(y);
     if (FMT == VG_FMT_P2TR) {
-        // stage 1 of the P2TR path: hand the even-Y internal key to stage 2 (taproot.cuh); MODE is applied there
+        // stage 1 of the P2TR path: hand the public key to stage 2 (taproot.cuh); MODE is applied there.
+        // VG_TAP_SCALAR: (x, y) as it is — stage 2 needs x for the tweak hash and the parity of y for the sign of the scalar;
+        // else the even-Y internal key (y negated when odd), to which stage 2 adds t*G.
         valid = valid && idx < P.limit;
-        fe ny; fe_neg(ny, y); fe_canon(ny);
-        const bool odd = (y.v[0] & 1u) != 0;
         VG_ASSERT(P, P.points != nullptr && idx < (unsigned long long)P.n_threads * 2ull * P.half, 6);
         uint32_t *o = P.points + idx * 16;
+#if VG_TAP_SCALAR
+        VG_UNROLL for (int l = 0; l < 8; l++) { o[l] = valid ? x.v[l] : 0u; o[8 + l] = valid ? y.v[l] : 0u; }
+#else
+        fe ny; fe_neg(ny, y); fe_canon(ny);
+        const bool odd = (y.v[0] & 1u) != 0;
         VG_UNROLL for (int l = 0; l < 8; l++) { o[l] = valid ? x.v[l] : 0u; o[8 + l] = valid ? (odd ? ny.v[l] : y.v[l]) : 0u; }
+#endif
         return;
     }
     uint32_t dg[VG_DIGEST_WORDS];

@@ -63,6 +63,7 @@ struct vg_scan_params {
     // P2TR only (taproot.cuh): stage 1 writes the even-Y internal key of window key i to points[16*i .. 16*i+15]
     // (x limbs, y limbs; all-zero = invalid), stage 2 adds t*G from tap_table[256/tap_bits][1 << tap_bits][16]
     uint32_t *points; const uint32_t *tap_table; uint32_t tap_bits;
+    uint32_t tap_base[8];     // scalar of window key 0 (little-endian limbs): stage 2 derives Q = (t +/- k) * G from the key's scalar
     // checked builds (-DVG_CHECKED, tools/check_build.sh): [0] = code of the first failed device-side bounds check, [1] = how many
     // failed. compute-sanitizer is closed on this pool, so the index arithmetic of every kernel carries its own asserts instead.
     uint32_t *violations;

@@ -4,11 +4,14 @@
 // TapTweak to the host: per key a tagged SHA-256 and a full scalar multiplication through
 // bitcoin::Address::p2tr (src/gpu.rs:1288-1290, src/address.rs:136-140). Here the whole derivation runs on the GPU:
 //
-//   stage 1 (walk kernel, FMT = P2TR): writes the even-Y internal key P = (x, y) of every key of the window into
+//   stage 1 (walk kernel, FMT = P2TR): writes the public key (x, y) of every key of the window into
 //           `points` (64 B per key, limb order as `fe`), all-zero for keys that are invalid / outside the range;
 //   stage 2 (this file): t = SHA256(SHA256("TapTweak") || SHA256("TapTweak") || x)   [one compression from a
 //           precomputed midstate, same constant as src/shaders/sha256.wgsl:177-249]
-//           Q = P + t*G through a fixed-base table tab[j][v] = v * 2^(bits*j) * G (bits = 16: 16 mixed additions,
+//           Q = P_even + t*G. The key's scalar k is known (window base + index), and P_even = k*G for even y, (n - k)*G for odd, so
+//           Q = s*G with s = t + k or t + n - k (mod n): ONE fixed-base multiplication, no addition of P (VG_TAP_SCALAR; with it off,
+//           stage 1 stores the even-Y point and stage 2 adds t*G to it: one table addition more per key).
+//           The multiplication runs through a fixed-base table tab[j][v] = v * 2^(bits*j) * G (bits = 16: 16 mixed additions,
 //           64 MiB, L2-resident; bits = 24: 11 additions, 11 GiB of HBM gathered at random), kept in Jacobian form; one field inversion per VG_TAP_GROUP keys (Montgomery's
 //           trick over the group's Z^2) turns X/Z^2 into the 32-byte witness program x(Q), which goes through the
 //           same matcher as the other formats (interval / exact / Bech32m-fed DFA).
@@ -39,6 +42,26 @@ VG_DEV bool vg_tweak_is_valid(const uint32_t t[8]) {
     uint32_t any = 0;
     VG_UNROLL for (int i = 0; i < 8; i++) any |= k[i];
     return any == 0 || scalar_is_valid(k);          // t == 0 is allowed by BIP341 (Q = P)
+}
+// r = n - k for 0 < k < n (little-endian limbs)
+VG_DEV void vg_scalar_neg_n(uint32_t r[8], const uint32_t k[8]) {
+    const uint32_t n[8] = {VG_N0, VG_N1, VG_N2, VG_N3, VG_N4, VG_N5, VG_N6, VG_N7};
+    SUB_CC(r[0], n[0], k[0]);
+    VG_UNROLL for (int i = 1; i < 7; i++) SUBC_CC(r[i], n[i], k[i]);
+    SUBC(r[7], n[7], k[7]);
+}
+// r = a + b mod n for a, b < n (little-endian limbs)
+VG_DEV void vg_scalar_add_mod_n(uint32_t r[8], const uint32_t a[8], const uint32_t b[8]) {
+    const uint32_t n[8] = {VG_N0, VG_N1, VG_N2, VG_N3, VG_N4, VG_N5, VG_N6, VG_N7};
+    uint32_t s[8], d[8], c, br;
+    ADD_CC(s[0], a[0], b[0]);
+    VG_UNROLL for (int i = 1; i < 8; i++) ADDC_CC(s[i], a[i], b[i]);
+    ADDC(c, 0u, 0u);                                   // a + b >= 2^256
+    SUB_CC(d[0], s[0], n[0]);
+    VG_UNROLL for (int i = 1; i < 8; i++) SUBC_CC(d[i], s[i], n[i]);
+    SUBC(br, 0u, 0u);                                  // 0xFFFFFFFF when s < n
+    const bool take = c != 0 || br == 0;               // the true sum is >= n
+    VG_UNROLL for (int i = 0; i < 8; i++) r[i] = take ? d[i] : s[i];
 }
 // r = a + (bx, by) for a finite Jacobian a, generic case only (8M + 3S, no calls). Returns false when the two points share
 // their x coordinate (doubling / opposite points): the caller then redoes the key with the complete formulas.
@@ -99,15 +122,21 @@ VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t j, uint32_t bits) {
     return (sh ? ((lo >> sh) | (hi << (32u - sh))) : lo) & mask;
 }
 
-// Q = P + t*G in Jacobian coordinates. Returns false when Q is the point at infinity (t*G = -P).
+// Q = P + t*G in Jacobian coordinates (VG_TAP_SCALAR: Q = t*G, P unused, t the full scalar). Returns false when Q is the point at infinity.
 // FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false);
 // q.y is then not computed for the top window (VG_TAP_LAST_NO_Y): only q.x and q.z are meaningful.
 // FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
 template <bool FAST>
 VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true, uint32_t *viol = nullptr) {
     (void)viol;
+#if VG_TAP_SCALAR
+    (void)px; (void)py;
+    fe_set_zero(q.x); fe_set_zero(q.y); fe_set_one(q.z); q.inf = true;
+    bool special = false, affine = false, have = false;      // have: q holds a point (the first non-zero digit's table entry, as it is)
+#else
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
-    bool special = false, affine = true;        // affine: q.z is still 1
+    bool special = false, affine = true, have = true;        // affine: q.z is still 1
+#endif
     const uint32_t n_win = vg_tap_windows(bits), mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
 #ifndef VG_HOST_EMU
     #pragma unroll 1
@@ -129,13 +158,14 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
         bx.v[0] = a0.x; bx.v[1] = a0.y; bx.v[2] = a0.z; bx.v[3] = a0.w; bx.v[4] = a1.x; bx.v[5] = a1.y; bx.v[6] = a1.z; bx.v[7] = a1.w;
         by.v[0] = a2.x; by.v[1] = a2.y; by.v[2] = a2.z; by.v[3] = a2.w; by.v[4] = a3.x; by.v[5] = a3.y; by.v[6] = a3.z; by.v[7] = a3.w;
 #endif
+        if (!have) { q.x = bx; q.y = by; fe_set_one(q.z); q.inf = false; have = true; affine = true; continue; }
         if (FAST) {
             if (VG_TAP_FIRST_AFFINE && affine) { if (!vg_aff_add_affine_fast(q, bx, by)) special = true; affine = false; }
             else if (!vg_gej_add_affine_fast(q, bx, by, !VG_TAP_LAST_NO_Y || j + 1 < n_win)) special = true;
         }
         else { gej_t r; gej_add_affine(r, q, bx, by); q = r; if (q.inf) { fe_set_one(q.z); } }
     }
-    return !q.inf && !special;
+    return have && !q.inf && !special;
 }
 
 VG_COLD bool vg_tap_output_key_slow(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
@@ -174,6 +204,17 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
             uint32_t t[8];
             vg_taptweak_hash(t, px);
             ok = ok && vg_tweak_is_valid(t);
+#if VG_TAP_SCALAR
+            {   // t <- s = t + k (even y) or t + n - k (odd y) mod n, k = window base + key index; s == 0: Q would be infinity
+                uint32_t kk[8], tl[8], sl[8], any = 0;
+                scalar_add_u64(kk, P.tap_base, first + (unsigned long long)k);
+                if (py.v[0] & 1u) vg_scalar_neg_n(kk, kk);
+                VG_UNROLL for (int i = 0; i < 8; i++) tl[i] = t[7 - i];
+                vg_scalar_add_mod_n(sl, tl, kk);
+                VG_UNROLL for (int i = 0; i < 8; i++) { t[7 - i] = sl[i]; any |= sl[i]; }
+                ok = ok && any != 0;
+            }
+#endif
             gej_t q;
             // all threads walk the table loop together (barriers inside); invalid keys skip the additions
             if (!vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits, ok, P.violations) && ok)
