@@ -420,6 +420,25 @@ def test_hit_buffer_overflow_is_rescanned(monkeypatch):
         r.close()
 
 
+def test_big_text_records_are_copied_out_whole(small_runner):
+    """Tens of thousands of hits: the records reach the caller through a bytes object the library fills on several threads
+    (vgen_cuda_scan_fetch_text with the exact size; gpu.py fetch_text). Same bytes as the library's own blob, every record right."""
+    start, n = 2**64 + 777, 1 << 15
+    res = _scan(small_runner, "p2pkh", "^1", start, n)                       # every P2PKH address starts with 1
+    assert len(res.matches) == n and res.operations == n
+    ptr, ln = C.c_void_p(), C.c_uint64(0)
+    L = small_runner._lib
+    assert L.vgen_cuda_scan_text(small_runner._ctx, C.cast(C.byref(ptr), C.POINTER(C.c_char_p)), C.byref(ln)) == 1
+    blob = C.string_at(ptr, ln.value)
+    assert ln.value > (4 << 20)                                              # large enough for the threaded copy
+    text, got = small_runner.fetch_text(n)
+    assert got == n and bytes(text) == blob
+    for i in (0, 1, 4097, n // 2, n - 2, n - 1):
+        m = res.matches[i]
+        a, w, _ = oracle.address("p2pkh", start + i)
+        assert (int(m.hex, 16), m.address, m.wif) == (start + i, a, w)
+
+
 def test_two_lanes_per_gpu_cover_the_range_once(runner):
     """Every GPU is driven through 2 lanes (streams) taking alternate windows: the union is the range, each key once."""
     assert runner.lane_count() == 2 * len(runner.devices)

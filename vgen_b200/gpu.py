@@ -219,6 +219,13 @@ class GpuRunner:
         # fast path: the scan's confirm workers already built every record; one copy out of the library's buffer
         ptr, ln = C.c_void_p(), C.c_uint64(0)
         if self._lib.vgen_cuda_scan_text(self._ctx, C.cast(C.byref(ptr), C.POINTER(C.c_char_p)), C.byref(ln)):
+            if ln.value >= _BIG_TEXT:
+                # tens of MB: a new bytes object filled by the library on several threads instead of one memcpy here
+                obj = _bytes_new(None, ln.value)
+                nw = C.c_uint64(0)
+                nb = int(self._lib.vgen_cuda_scan_fetch_text(self._ctx, 0, total, _bytes_addr(obj), ln.value + 1, C.byref(nw)))
+                if nb == ln.value and nw.value == total:
+                    return obj, total
             return C.string_at(ptr, ln.value), total
         cap = min(total * 227 + 1, 1 << 28)               # 227 = the library's bound for one record
         store = bytearray(cap)
@@ -287,6 +294,14 @@ def plan_windows(start, end, global_lanes, lane, sm_count=148, keys_per_launch_h
     L.vgen_plan_windows(_be(start), _be(end), sm_count, keys_per_launch_hint, global_lanes, lane, int(can_end_early), keys, lens, n)
     raw = keys.raw
     return [(int.from_bytes(raw[32 * i:32 * i + 32], "big"), int(lens[i])) for i in range(n)]
+
+
+# bytes objects the library fills in place (PyBytes_FromStringAndSize(NULL, n): n bytes, uninitialised, plus the trailing NUL)
+_BIG_TEXT = 1 << 20
+_bytes_new = C.pythonapi.PyBytes_FromStringAndSize
+_bytes_new.restype, _bytes_new.argtypes = C.py_object, [C.c_void_p, C.c_ssize_t]
+_bytes_addr = C.pythonapi.PyBytes_AsString
+_bytes_addr.restype, _bytes_addr.argtypes = C.c_void_p, [C.py_object]
 
 
 class DigestBatch(collections.abc.Sequence):
