@@ -117,6 +117,8 @@ int emu_confirm_eth_fold(const uint32_t *dg, const uint16_t *table, const uint8_
 // fixed-base table (4 keeps the host build cheap).
 static std::vector<uint32_t> g_tap; static uint32_t g_tap_bits = 0;
 int emu_tap_scalar_form() { return VG_TAP_SCALAR; }
+void emu_scalar_add_mod_n(const uint32_t *a, const uint32_t *b, uint32_t *r) { vg_scalar_add_mod_n(r, a, b); }
+void emu_scalar_neg_n(const uint32_t *k, uint32_t *r) { vg_scalar_neg_n(r, k); }
 void emu_tap_stage2(uint32_t *points, const uint32_t *base8, uint32_t n, uint32_t bits, uint8_t *out32) {
     ensure_pow2();
     if (g_tap_bits != bits) {

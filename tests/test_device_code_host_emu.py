@@ -136,6 +136,24 @@ def test_p2tr_two_stage_vs_oracle(emu):
         assert out.raw == want[:32 * total], start
 
 
+def test_p2tr_scalar_arithmetic_mod_n(emu):
+    """taproot.cuh vg_scalar_add_mod_n / vg_scalar_neg_n (s = t + k or t + n - k mod n): the cases hashing never produces —
+    sums that reach n exactly, pass 2^256, or come out 0 — and random operands, against Python integers."""
+    rng = random.Random(341)
+    pairs = [(0, 0), (N - 1, 1), (N - 1, N - 1), (1, N - 2), (N - 2**128, 2**128), (2**255, 2**255), (N - 1, 2**256 - N),
+             (2**256 - N, 2**256 - N), (N // 2, N // 2), (N // 2, N // 2 + 1), (0, N - 1)]
+    pairs += [(rng.randrange(N), rng.randrange(N)) for _ in range(2000)]
+    pairs += [(N - 1 - rng.randrange(2**40), N - 1 - rng.randrange(2**40)) for _ in range(200)]
+    for a, b in pairs:
+        r = (C.c_uint32 * 8)()
+        emu.emu_scalar_add_mod_n(limbs(a), limbs(b), r)
+        assert val(r) == (a + b) % N, (hex(a), hex(b))
+    for k in [1, 2, N - 1, N - 2, N // 2, 2**255, 2**128] + [rng.randrange(1, N) for _ in range(500)]:
+        r = (C.c_uint32 * 8)()
+        emu.emu_scalar_neg_n(limbs(k), r)
+        assert val(r) == N - k
+
+
 def test_p2tr_stage2_invalid_points_and_small_tweak_table(emu):
     """Stage 2 alone: 64 consecutive scalars from several bases, their public keys as stage 1 stores them (the scalar form reads
     x, the parity of y and derives the key's scalar from the window base; the older form wants the even-Y point). All-zero points
