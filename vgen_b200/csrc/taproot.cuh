@@ -122,13 +122,50 @@ VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t j, uint32_t bits) {
     return (sh ? ((lo >> sh) | (hi << (32u - sh))) : lo) & mask;
 }
 
-// Q = P + t*G in Jacobian coordinates (VG_TAP_SCALAR: Q = t*G, P unused, t the full scalar). Returns false when Q is the point at infinity.
-// FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false);
-// q.y is then not computed for the top window (VG_TAP_LAST_NO_Y): only q.x and q.z are meaningful.
+// The accumulator of the fast path in XYZZ coordinates (x = X / ZZ, y = Y / ZZZ, ZZ^3 = ZZZ^2): a mixed addition costs 8M + 2S
+// instead of the Jacobian 8M + 3S, the top window (no Y3, no ZZZ3) 5M + 2S instead of 6M + 3S, and the caller gets ZZ = Z^2, which
+// is what the grouped inversion wants, without a squaring. VG_TAP_XYZZ = 0: Jacobian accumulator.
+#ifndef VG_TAP_XYZZ
+#define VG_TAP_XYZZ 1
+#endif
+// (X, Y, ZZ, ZZZ) += (bx, by), generic case only; false when the two points share their x coordinate
+VG_DEV bool vg_xyzz_add_affine_fast(fe &X, fe &Y, fe &ZZ, fe &ZZZ, const fe &bx, const fe &by, bool need_y) {
+    fe u2, s2, p, r, pp, ppp, q, t;
+    fe_mul(u2, bx, ZZ); fe_mul(s2, by, ZZZ);
+    fe_sub(p, u2, X); fe_sub(r, s2, Y);
+    fe pc = p; fe_canon(pc);
+    if (fe_is_zero_raw(pc)) return false;
+    fe_sqr_fast(pp, p); fe_mul(ppp, pp, p); fe_mul(q, X, pp);
+    fe_sqr_fast(t, r); fe_sub(t, t, ppp); fe_sub(t, t, q); fe_sub(t, t, q);      // X3
+    if (need_y) { fe_sub(q, q, t); fe_mul(q, r, q); fe_mul(u2, Y, ppp); fe_sub(Y, q, u2); fe_mul(ZZZ, ZZZ, ppp); }
+    X = t;
+    fe_mul(ZZ, ZZ, pp);
+    return true;
+}
+// the same for an affine accumulator (ZZ = ZZZ = 1): 4M + 2S
+VG_DEV bool vg_xyzz_add_affine_first(fe &X, fe &Y, fe &ZZ, fe &ZZZ, const fe &bx, const fe &by) {
+    fe p, r, q, t, u;
+    fe_sub(p, bx, X); fe_sub(r, by, Y);
+    fe pc = p; fe_canon(pc);
+    if (fe_is_zero_raw(pc)) return false;
+    fe_sqr_fast(ZZ, p); fe_mul(ZZZ, ZZ, p); fe_mul(q, X, ZZ);
+    fe_sqr_fast(t, r); fe_sub(t, t, ZZZ); fe_sub(t, t, q); fe_sub(t, t, q);      // X3
+    fe_sub(q, q, t); fe_mul(q, r, q); fe_mul(u, Y, ZZZ); fe_sub(Y, q, u);
+    X = t;
+    return true;
+}
+
+// Q = P + t*G (VG_TAP_SCALAR: Q = t*G, P unused, t the full scalar) as qx = X and qzz = Z^2 of a projective representative
+// (x(Q) = qx / qzz). Returns false when Q is the point at infinity.
+// FAST = true: generic-case additions only; returns false at the first special case (the caller falls back to FAST = false).
 // FAST = false: gej_add_affine handles every special case (equal points -> doubling, opposite points -> infinity).
 template <bool FAST>
-VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true, uint32_t *viol = nullptr) {
+VG_DEV bool vg_tap_output_key(fe &qx, fe &qzz, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits, bool active = true, uint32_t *viol = nullptr) {
     (void)viol;
+    gej_t q;
+#if VG_TAP_XYZZ
+    fe zzz; fe_set_one(zzz);                    // fast path: q.z holds ZZ
+#endif
 #if VG_TAP_SCALAR
     (void)px; (void)py;
     fe_set_zero(q.x); fe_set_zero(q.y); fe_set_one(q.z); q.inf = true;
@@ -160,16 +197,23 @@ VG_DEV bool vg_tap_output_key(gej_t &q, const fe &px, const fe &py, const uint32
 #endif
         if (!have) { q.x = bx; q.y = by; fe_set_one(q.z); q.inf = false; have = true; affine = true; continue; }
         if (FAST) {
+#if VG_TAP_XYZZ
+            if (affine) { if (!vg_xyzz_add_affine_first(q.x, q.y, q.z, zzz, bx, by)) special = true; affine = false; }
+            else if (!vg_xyzz_add_affine_fast(q.x, q.y, q.z, zzz, bx, by, !VG_TAP_LAST_NO_Y || j + 1 < n_win)) special = true;
+#else
             if (VG_TAP_FIRST_AFFINE && affine) { if (!vg_aff_add_affine_fast(q, bx, by)) special = true; affine = false; }
             else if (!vg_gej_add_affine_fast(q, bx, by, !VG_TAP_LAST_NO_Y || j + 1 < n_win)) special = true;
+#endif
         }
         else { gej_t r; gej_add_affine(r, q, bx, by); q = r; if (q.inf) { fe_set_one(q.z); } }
     }
+    qx = q.x;
+    if (FAST && VG_TAP_XYZZ) qzz = q.z; else fe_sqr_fast(qzz, q.z);
     return have && !q.inf && !special;
 }
 
-VG_COLD bool vg_tap_output_key_slow(gej_t &q, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
-    return vg_tap_output_key<false>(q, px, py, t, tab, bits);
+VG_COLD bool vg_tap_output_key_slow(fe &qx, fe &qzz, const fe &px, const fe &py, const uint32_t t[8], const uint32_t *tab, uint32_t bits) {
+    return vg_tap_output_key<false>(qx, qzz, px, py, t, tab, bits);
 }
 
 // stage-2 thread: keys [first, first + VG_TAP_GROUP) of the window
@@ -215,11 +259,11 @@ VG_DEV void vg_tap_thread(const vg_scan_params &P, const vg_dfa_view &dv, unsign
                 ok = ok && any != 0;
             }
 #endif
-            gej_t q;
+            fe qx, qzz;
             // all threads walk the table loop together (barriers inside); invalid keys skip the additions
-            if (!vg_tap_output_key<true>(q, px, py, t, P.tap_table, P.tap_bits, ok, P.violations) && ok)
-                ok = vg_tap_output_key_slow(q, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
-            if (ok) { X[k] = q.x; fe_sqr_fast(z2, q.z); }
+            if (!vg_tap_output_key<true>(qx, qzz, px, py, t, P.tap_table, P.tap_bits, ok, P.violations) && ok)
+                ok = vg_tap_output_key_slow(qx, qzz, px, py, t, P.tap_table, P.tap_bits);      // special case met (practically never)
+            if (ok) { X[k] = qx; z2 = qzz; }
         }
         if (ok) ok_mask |= 1ull << k;
         Z2[k] = z2;
