@@ -19,14 +19,17 @@ N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
 P_FIELD = 2**256 - 2**32 - 977
 
 
-@pytest.fixture(scope="module")
-def emu():
+# The device headers are compiled for the host twice: as every format but P2TR builds them, and with the switches scan_fmt.inc sets
+# for the P2TR translation unit (36-product squarings inside the inversion, the reduction's odd-limb products in their own pairs).
+@pytest.fixture(scope="module", params=["default", "p2tr-build"])
+def emu(request):
     csrc = os.path.join(HERE, "..", "vgen_b200", "csrc")
     deps = [SRC] + [os.path.join(csrc, f) for f in ("fe.cuh", "ec.cuh", "hash.cuh", "scan_core.cuh", "match.cuh", "taproot.cuh", "scan_types.h", "kernels.h")]
     deps = [d for d in deps if os.path.exists(d)]
-    if not os.path.exists(LIB) or any(os.path.getmtime(d) > os.path.getmtime(LIB) for d in deps):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", "-fPIC", "-shared", "-o", LIB, SRC])
-    return C.CDLL(LIB)
+    lib, flags = (LIB, []) if request.param == "default" else (LIB.replace(".so", "_p2tr.so"), ["-DVG_INV_FAST_SQR=1", "-DVG_REDUCE_SPLIT=1"])
+    if not os.path.exists(lib) or any(os.path.getmtime(d) > os.path.getmtime(lib) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", "-fPIC", "-shared"] + flags + ["-o", lib, SRC])
+    return C.CDLL(lib)
 
 
 def limbs(v):

@@ -143,11 +143,24 @@ VG_DEV void fe_reduce_wide(fe &r, const uint32_t t[16]) {
     MADC_LO_CC(lo[4], h[4], FE_RC_LO, lo[4]); MADC_HI_CC(lo[5], h[4], FE_RC_LO, lo[5]);
     MADC_LO_CC(lo[6], h[6], FE_RC_LO, lo[6]); MADC_HI_CC(lo[7], h[6], FE_RC_LO, lo[7]);
     ADDC(lo[8], lo[8], 0u);
+#if defined(VG_REDUCE_SPLIT) && VG_REDUCE_SPLIT
+    {   // the odd limbs' products in their own aligned pairs (no addend, no carry: four independent wide products), then ONE add chain
+        // shifted by a limb. Accumulating them straight into lo[1..8] makes ptxas copy lo[] into pairs of the other alignment and
+        // back (16 IMAD.MOV on the multiplier pipe per reduction). Measured on the P2TR stage, where that pipe binds: 1,045 fewer
+        // IMAD.MOV in the kernel, yet 872 against 878 Mkeys/s (profiles/reduce_split_r02.log), so the switch stays off.
+        uint32_t od[8];
+        VG_UNROLL for (int k = 0; k < 4; k++) { MAD_LO_CC(od[2 * k], h[2 * k + 1], FE_RC_LO, 0u); MADC_HI(od[2 * k + 1], h[2 * k + 1], FE_RC_LO, 0u); }
+        ADD_CC(lo[1], lo[1], od[0]);
+        VG_UNROLL for (int k = 1; k < 8; k++) ADDC_CC(lo[k + 1], lo[k + 1], od[k]);
+        ADDC(lo[9], lo[9], 0u);
+    }
+#else
     MAD_LO_CC(lo[1], h[1], FE_RC_LO, lo[1]); MADC_HI_CC(lo[2], h[1], FE_RC_LO, lo[2]);
     MADC_LO_CC(lo[3], h[3], FE_RC_LO, lo[3]); MADC_HI_CC(lo[4], h[3], FE_RC_LO, lo[4]);
     MADC_LO_CC(lo[5], h[5], FE_RC_LO, lo[5]); MADC_HI_CC(lo[6], h[5], FE_RC_LO, lo[6]);
     MADC_LO_CC(lo[7], h[7], FE_RC_LO, lo[7]); MADC_HI_CC(lo[8], h[7], FE_RC_LO, lo[8]);
     ADDC(lo[9], lo[9], 0u);
+#endif
     // + hi * 2^32
     ADD_CC(lo[1], lo[1], h[0]);
     VG_UNROLL for (int i = 1; i < 8; i++) ADDC_CC(lo[i + 1], lo[i + 1], h[i]);
