@@ -121,14 +121,18 @@ void emu_scalar_add_mod_n(const uint32_t *a, const uint32_t *b, uint32_t *r) { v
 void emu_scalar_neg_n(const uint32_t *k, uint32_t *r) { vg_scalar_neg_n(r, k); }
 void emu_tap_stage2(uint32_t *points, const uint32_t *base8, uint32_t n, uint32_t bits, uint8_t *out32) {
     ensure_pow2();
-    if (g_tap_bits != bits) {
-        const size_t cnt = (size_t)vg_tap_windows(bits) << bits;
-        g_tap.assign(cnt * 16, 0);
-        for (size_t i = 0; i < cnt; i++) {
-            uint32_t j = (uint32_t)(i >> bits), v = (uint32_t)(i & ((1u << bits) - 1)), k[8];
-            if (!vg_tap_digit_scalar(k, j, v, bits)) continue;
-            fe x, y; scalar_mul_pow2(x, y, k, g_pow2.data());
-            memcpy(&g_tap[i * 16], x.v, 32); memcpy(&g_tap[i * 16 + 8], y.v, 32);
+    if (g_tap_bits != bits) {          // bits: a geometry word (scan_types.h): plain 4..26, or VG_TAP_SIGNED | n_hi << 8 | W
+        g_tap.assign((size_t)vg_tap_entries(bits) * 16, 0);
+        for (uint32_t j = 0; j < vg_tap_windows(bits); j++) {
+            uint32_t off, width, o2, w2; unsigned long long first, next;
+            vg_tap_window(bits, j, &off, &width, &first);
+            vg_tap_window(bits, j + 1, &o2, &w2, &next);
+            for (unsigned long long i = first; i < next; i++) {
+                uint32_t k[8];
+                if (!vg_tap_digit_scalar(k, off, (uint32_t)(i - first))) continue;
+                fe x, y; scalar_mul_pow2(x, y, k, g_pow2.data());
+                memcpy(&g_tap[i * 16], x.v, 32); memcpy(&g_tap[i * 16 + 8], y.v, 32);
+            }
         }
         g_tap_bits = bits;
     }

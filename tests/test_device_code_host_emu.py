@@ -177,7 +177,10 @@ def test_p2tr_stage2_invalid_points_and_small_tweak_table(emu):
                     pts[16 * i + 8 + l] = (y >> (32 * l)) & 0xffffffff
                 live.append(i)
         assert live
-        for bits in (4, 8, 5, 7):       # 5 and 7: digits straddle 32-bit limbs and the top window is partial (as with 24-bit windows)
+        SIGNED = 0x40000000
+        # 5 and 7: digits straddle 32-bit limbs and the top window is partial (as with 24-bit windows). Signed geometries
+        # (scan_types.h: W | n_hi << 8; widths add up to 256): 64 x 4 bits, 1 x 6 + 50 x 5, 4 x 8 + 32 x 7 (the shape of the 9-window table)
+        for bits in (4, 8, 5, 7, SIGNED | 4, SIGNED | (1 << 8) | 5, SIGNED | (4 << 8) | 7):
             out = C.create_string_buffer(32 * n)
             emu.emu_tap_stage2(pts, limbs(base), n, bits, out)
             for i, k in enumerate(ks):

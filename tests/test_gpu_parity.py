@@ -245,6 +245,24 @@ def test_p2tr_long_job_builds_the_wide_table(runner):
     assert "VGEN_TAP_BITS" in os.environ or runner.tap_bits() == 24
 
 
+@pytest.mark.parametrize("geom", ["s7.4", "s5.1", "s4.0", "13"])
+def test_p2tr_table_geometries(monkeypatch, geom):
+    """The tweak stage's fixed-base table in other geometries (scan_types.h; VGEN_TAP_BITS): signed mixed-radix windows — the shape
+    of the 111.7 GB 9-window table for the longest jobs, here with 36, 51 and 64 small windows — and an odd plain width. Witness
+    programs equal to the oracle's at both ends of the scalar range; a scan finds the oracle's matches."""
+    monkeypatch.setenv("VGEN_TAP_BITS", geom)
+    r = vg.GpuRunner(vg.DEFAULT_BATCH_SIZE)
+    try:
+        for start, n in ((1, 3000), (2**200 + 12345, 3000), (N - 2000, 3000)):
+            got = r.digest_batch("p2tr", start, n)
+            assert got == oracle.digest_batch("p2tr", start, n), (geom, hex(start))
+        want_bits = (0x40000000 | (int(geom[1:].split(".")[1]) << 8) | int(geom[1:].split(".")[0])) if geom[0] == "s" else int(geom)
+        assert r.tap_bits() == want_bits
+        _check_scan(r, "p2tr", "^bc1pq", 2**64, 1 << 14)
+    finally:
+        r.close()
+
+
 def test_config_c1_full_match_set(runner):
     """BASELINE.json config C1: 2^24-key window from 2^64, P2PKH, ^1Cat — full match set vs the oracle."""
     res = _check_scan(runner, "p2pkh", "^1Cat", 2**64, 1 << 24)

@@ -241,19 +241,28 @@ bool Engine::upload_dfa(std::string &err) {
     return true;
 }
 
-// Window width of the P2TR fixed-base table (taproot.cuh), chosen per job (measured on B200, profiles/tap_bits_r01.log):
-//   16 bits: 16 windows x 65,536 x 64 B = 64 MiB, built in 2 ms; 16 additions per key                      476 Mkeys/s
-//   24 bits: 11 windows x 2^24 x 64 B = 11 GiB of the 180 GB HBM, built in 0.15 s; 11 additions per key     638 Mkeys/s
-//   26 bits: 10 windows x 2^26 x 64 B = 40 GiB, built in 0.43 s; 10 additions per key                       683 Mkeys/s
+// Geometry of the P2TR fixed-base table (scan_types.h), chosen per job (measured on B200, profiles/tap_bits_r01.log, tap_signed_r02.log):
+//   16 bits: 16 windows x 65,536 x 64 B = 64 MiB, built in 2 ms; 16 table lookups per key
+//   24 bits: 11 windows x 2^24 x 64 B = 11 GiB of the 180 GB HBM, built in 0.15 s; 11 lookups
+//   26 bits: 10 windows x 2^26 x 64 B = 40 GiB, built in 0.43 s; 10 lookups
+//   signed 4 x 29 + 5 x 28 bits: 9 windows, 1.745 G entries = 111.7 GB; 9 lookups
 // The entries are gathered at random from DRAM either way (ncu: the 64 MiB table is flushed out of L2 by the window's point
-// stream), so a wider table only saves additions. Jobs of >= 2^30 keys take 24 bits, >= 2^36 keys 26 bits (when the
-// device has the room). VGEN_TAP_BITS (4..26) forces a width.
+// stream), so a wider table only saves additions. Jobs of >= 2^30 keys take 24 bits, >= 2^36 keys 26 bits, >= 2^38 keys the
+// signed 9-window table (each when the device has the room). VGEN_TAP_BITS forces a geometry: 4..26, or sW.H for the signed
+// one with H windows of W + 1 bits and the rest of W bits (s28.4 is the 9-window table; small ones for tests).
 static uint32_t tap_bits_for(uint64_t keys_hint) {
-    static const char *e = getenv("VGEN_TAP_BITS");
-    if (e) { long v = strtol(e, nullptr, 10); return (uint32_t)(v < 4 ? 4 : v > 26 ? 26 : v); }
-    return keys_hint >= (1ull << 36) ? 26u : keys_hint >= (1ull << 30) ? 24u : 16u;
+    if (const char *e = getenv("VGEN_TAP_BITS")) {
+        if (e[0] == 's' || e[0] == 'S') {
+            unsigned W = 0, H = 0;
+            if (sscanf(e + 1, "%u.%u", &W, &H) >= 1 && W < 256 && H < 256 && vg_tap_geom_valid(VG_TAP_GEOM_SIGNED(W, H))) return VG_TAP_GEOM_SIGNED(W, H);
+            return 16u;
+        }
+        long v = strtol(e, nullptr, 10);
+        return (uint32_t)(v < 4 ? 4 : v > 26 ? 26 : v);
+    }
+    return keys_hint >= (1ull << 38) ? VG_TAP_GEOM_SIGNED(28, 4) : keys_hint >= (1ull << 36) ? 26u : keys_hint >= (1ull << 30) ? 24u : 16u;
 }
-static size_t tap_table_bytes(uint32_t bits) { return ((size_t)((256 + bits - 1) / bits) << bits) * 64; }
+static size_t tap_table_bytes(uint32_t geom) { return (size_t)vg_tap_entries(geom) * 64; }
 
 // P2TR needs two more buffers: the stage-1 -> stage-2 point buffer of every lane (64 B per window key) and the fixed-base
 // table of the tweak addition (one per GPU, shared by its lanes). Allocated and built on first use; a wider table replaces
@@ -273,6 +282,7 @@ bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
         CK(cudaSetDevice(D.device));
         CK(cudaMemGetInfo(&free_b, &total_b));
         const size_t held = tap_bits_ ? tap_table_bytes(tap_bits_) : 0;      // freed before the new one is allocated
+        if (want > 26 && free_b + held < tap_table_bytes(want) + (8ull << 30)) want = 26;      // > 26: a signed geometry word
         if (want > 24 && free_b + held < tap_table_bytes(want) + (8ull << 30)) want = 24;
         if (want > 16 && free_b + held < tap_table_bytes(want) + (4ull << 30)) want = 16;
     }
@@ -290,7 +300,7 @@ bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
     for (auto &D : devices_) { if (D.failed) continue; CK(cudaSetDevice(D.device)); CK(cudaStreamSynchronize(lanes_[D.lanes[0]].stream)); }
     tap_bits_ = want;
     if (getenv("VGEN_TRACE"))
-        fprintf(stderr, "[vgen trace] tap table %u bits     %9.3f ms\n", want, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+        fprintf(stderr, "[vgen trace] tap table 0x%x (%u windows, %.1f GB) %9.3f ms\n", want, vg_tap_windows(want), tap_table_bytes(want) / 1e9, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
     return true;
 }
 

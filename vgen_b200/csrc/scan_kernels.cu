@@ -49,18 +49,19 @@ __global__ void k_build_gtab(uint32_t *gtab, uint32_t half, const uint32_t *pow2
     for (int l = 0; l < 8; l++) { gtab[i * 16 + l] = x.v[l]; gtab[i * 16 + 8 + l] = y.v[l]; }
 }
 
-// tab[j][v][16] = (v << (bits*j)) * G for the P2TR tweak addition; v = 0 entries are never read (all-zero).
-// One thread builds VG_TAPB_GROUP consecutive digits of one window: the first by 8-bit windowed multiplication kept in
-// Jacobian form, the others by adding B = 2^(bits*j) * G, and one field inversion turns the group into affine points
+// One window of the P2TR fixed-base table (geometry: scan_types.h): win[v][16] = (v << off) * G for v < cnt; v = 0 is never read
+// (all-zero). One thread builds VG_TAPB_GROUP consecutive digits: the first by 8-bit windowed multiplication kept in
+// Jacobian form, the others by adding B = 2^off * G, and one field inversion turns the group into affine points
 // (the 24-bit table has 1.8e8 entries: an inversion per entry made its build 2.4 s). Digits of a partial top window that
 // would overflow 2^256 are never read; they are filled with whatever the addition chain gives.
 #define VG_TAPB_GROUP 16
-__global__ void k_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *gtable) {
-    const unsigned long long n = (unsigned long long)vg_tap_windows(bits) << bits;
+__global__ void k_build_tap_table(uint32_t *win, unsigned long long cnt, uint32_t off, const uint32_t *gtable) {
+    const unsigned long long n = cnt;
     const unsigned long long i0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * VG_TAPB_GROUP;
     if (i0 >= n) return;
-    const uint32_t j = (uint32_t)(i0 >> bits), v0 = (uint32_t)(i0 & ((1ull << bits) - 1));
-    const uint32_t bit = j * bits, wi = bit >> 5, sh = bit & 31u;      // bit < 256
+    uint32_t *tab = win;
+    const uint32_t v0 = (uint32_t)i0;
+    const uint32_t bit = off, wi = bit >> 5, sh = bit & 31u;      // bit < 256
     uint32_t k[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     k[wi] = v0 << sh;
     if (sh != 0 && wi + 1 < 8) k[wi + 1] = v0 >> (32u - sh);
@@ -129,11 +130,18 @@ cudaError_t launch_build_tables(uint32_t *pow2, uint32_t *gtab, uint32_t half, c
     k_build_gtab<<<(half + 127) / 128, 128, 0, s>>>(gtab, half, pow2);
     return cudaGetLastError();
 }
-cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t bits, const uint32_t *pow2, cudaStream_t s) {
-    const unsigned long long n = (unsigned long long)((256u + bits - 1u) / bits) << bits;
-    const unsigned long long threads = (n + VG_TAPB_GROUP - 1) / VG_TAPB_GROUP;
-    k_build_tap_table<<<(unsigned)((threads + 127) / 128), 128, 0, s>>>(tab, bits, pow2);      // pow2: the full generator table (pow2 + win8)
-    return cudaGetLastError();
+cudaError_t launch_build_tap_table(uint32_t *tab, uint32_t geom, const uint32_t *pow2, cudaStream_t s) {
+    if (!vg_tap_geom_valid(geom)) return cudaErrorInvalidValue;
+    const uint32_t n_win = vg_tap_windows(geom);
+    for (uint32_t j = 0; j < n_win; j++) {          // one launch per window (at most 64 of them)
+        uint32_t off, width, off2, width2; unsigned long long first, next;
+        vg_tap_window(geom, j, &off, &width, &first);
+        vg_tap_window(geom, j + 1, &off2, &width2, &next);
+        const unsigned long long cnt = next - first, threads = (cnt + VG_TAPB_GROUP - 1) / VG_TAPB_GROUP;
+        k_build_tap_table<<<(unsigned)((threads + 127) / 128), 128, 0, s>>>(tab + first * 16, cnt, off, pow2);      // pow2: the full generator table (pow2 + win8)
+        VG_CK(cudaGetLastError());
+    }
+    return cudaSuccess;
 }
 cudaError_t launch_dump_points_x(const vg_scan_params &P, cudaStream_t s) {
     if (P.limit == 0) return cudaSuccess;

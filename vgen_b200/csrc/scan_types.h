@@ -9,6 +9,47 @@ enum { VG_MODE_MATCH = 0, VG_MODE_DUMP = 1 };
 #define VG_MAX_INTERVALS 32
 #define VG_DIGEST_WORDS 8
 
+// ---- geometry of the P2TR fixed-base table (taproot.cuh), shared by the kernels and the host engine ----
+// The geometry word `g` (vg_scan_params::tap_bits):
+//   plain  (VG_TAP_SIGNED clear): uniform unsigned windows of g bits; window j, digit v at entry (j << g) + v holds v * 2^(g*j) * G.
+//   signed (VG_TAP_SIGNED set)  : W = g & 0xff, n_hi = (g >> 8) & 0xff: the first n_hi windows are W + 1 bits wide, the others W, and
+//          their widths add up to exactly 256. Digits are signed, |d| <= 2^(width-1); a window holds the 2^(width-1) + 1 multiples
+//          0 .. 2^(width-1) of its base point and a negative digit takes the entry with y negated: half the entries per window,
+//          which is what lets 9 windows (4 x 29 + 5 x 28 bits) fit: 1.745 G entries = 111.7 GB of the 180 GB.
+#if defined(__CUDACC__)
+#define VG_HD __host__ __device__ __forceinline__
+#else
+#define VG_HD static inline
+#endif
+#define VG_TAP_SIGNED 0x40000000u
+#define VG_TAP_GEOM_SIGNED(W, n_hi) (VG_TAP_SIGNED | ((uint32_t)(n_hi) << 8) | (uint32_t)(W))
+VG_HD uint32_t vg_tap_windows(uint32_t g) {
+    if (g & VG_TAP_SIGNED) return (256u - ((g >> 8) & 0xffu)) / (g & 0xffu);
+    return (256u + g - 1u) / g;
+}
+// window j (j == number of windows: one past the end): its first bit, its width and the table index of its entry 0
+VG_HD void vg_tap_window(uint32_t g, uint32_t j, uint32_t *off, uint32_t *width, unsigned long long *first) {
+    if (g & VG_TAP_SIGNED) {
+        const uint32_t W = g & 0xffu, nh = (g >> 8) & 0xffu, jh = j < nh ? j : nh;
+        *width = W + (j < nh ? 1u : 0u);
+        *off = j * W + jh;
+        *first = (unsigned long long)jh * ((1ull << W) + 1ull) + (unsigned long long)(j - jh) * ((1ull << (W - 1u)) + 1ull);
+    } else { *width = g; *off = j * g; *first = (unsigned long long)j << g; }
+}
+VG_HD unsigned long long vg_tap_entries(uint32_t g) {
+    uint32_t off, width; unsigned long long first;
+    vg_tap_window(g, vg_tap_windows(g), &off, &width, &first);
+    return first;
+}
+// is g a geometry the kernels can run?
+VG_HD int vg_tap_geom_valid(uint32_t g) {
+    if (g & VG_TAP_SIGNED) {
+        const uint32_t W = g & 0xffu, nh = (g >> 8) & 0xffu;
+        return (g & ~(VG_TAP_SIGNED | 0xffffu)) == 0 && W >= 3u && W <= 30u && nh < 256u && (256u - nh) % W == 0u && nh <= (256u - nh) / W;
+    }
+    return g >= 4u && g <= 26u;
+}
+
 struct vg_hit_rec {          // 40 bytes
     uint32_t idx_lo, idx_hi; // key index inside the window
     uint32_t digest[VG_DIGEST_WORDS];   // digest bytes as little-endian words (byte 4i+j = byte j of digest[i])
@@ -61,7 +102,7 @@ struct vg_scan_params {
     uint32_t dfa_smem_bytes;  // shared-memory bytes for the DFA table + accept flags (0: read them from global memory)
     uint8_t *dump; uint32_t dump_stride;   // VG_MODE_DUMP: digest bytes per key index
     // P2TR only (taproot.cuh): stage 1 writes the even-Y internal key of window key i to points[16*i .. 16*i+15]
-    // (x limbs, y limbs; all-zero = invalid), stage 2 adds t*G from tap_table[256/tap_bits][1 << tap_bits][16]
+    // (x limbs, y limbs; all-zero = invalid), stage 2 walks tap_table (16 words per entry; geometry word tap_bits, see above)
     uint32_t *points; const uint32_t *tap_table; uint32_t tap_bits;
     uint32_t tap_base[8];     // scalar of window key 0 (little-endian limbs): stage 2 derives Q = (t +/- k) * G from the key's scalar
     // checked builds (-DVG_CHECKED, tools/check_build.sh): [0] = code of the first failed device-side bounds check, [1] = how many

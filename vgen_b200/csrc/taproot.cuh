@@ -101,25 +101,33 @@ VG_DEV bool vg_aff_add_affine_fast(gej_t &a, const fe &bx, const fe &by) {
     return true;
 }
 
-// Fixed-base table geometry: ceil(256 / bits) windows of 2^bits entries; window j, digit v holds (v * 2^(bits*j)) * G.
-// `bits` need not divide 32 or 256 (24-bit windows: 11 windows, the top one uses 16 bits).
-VG_DEV uint32_t vg_tap_windows(uint32_t bits) { return (256u + bits - 1u) / bits; }
-// k = v * 2^(bits*j) as 8 little-endian limbs; false when v is 0 or the product does not fit in 256 bits (unused entry)
-VG_DEV bool vg_tap_digit_scalar(uint32_t k[8], uint32_t j, uint32_t v, uint32_t bits) {
-    const uint32_t bit = j * bits, wi = bit >> 5, sh = bit & 31u;
+// Fixed-base table geometry: scan_types.h (vg_tap_windows / vg_tap_window / vg_tap_entries over the geometry word).
+// k = v * 2^off as 8 little-endian limbs; false when v is 0 or the product does not fit in 256 bits (unused entry)
+VG_DEV bool vg_tap_digit_scalar(uint32_t k[8], uint32_t off, uint32_t v) {
+    const uint32_t wi = off >> 5, sh = off & 31u;
     for (int i = 0; i < 8; i++) k[i] = 0;
-    if (v == 0 || bit >= 256u) return false;
-    if (bit + bits > 256u && (v >> (256u - bit)) != 0) return false;
+    if (v == 0 || off >= 256u) return false;
+    if (off + 32u > 256u && (v >> (256u - off)) != 0) return false;
     k[wi] = v << sh;
     if (sh != 0 && wi + 1 < 8) k[wi + 1] = v >> (32u - sh);
     return true;
 }
-// digit j of t (t as 8 big-endian words: word 7 is the least significant)
-VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t j, uint32_t bits) {
-    const uint32_t bit = j * bits, wi = bit >> 5, sh = bit & 31u, mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
+// the `width` bits of t from bit `off` up (t as 8 big-endian words: word 7 is the least significant; bits past 255 read as 0)
+VG_DEV uint32_t vg_tap_digit(const uint32_t t[8], uint32_t off, uint32_t width) {
+    const uint32_t wi = off >> 5, sh = off & 31u, mask = (width >= 32u) ? 0xffffffffu : ((1u << width) - 1u);
     uint32_t lo = 0, hi = 0;
     VG_UNROLL for (int i = 0; i < 8; i++) { lo = (wi == (uint32_t)i) ? t[7 - i] : lo; hi = (wi + 1u == (uint32_t)i) ? t[7 - i] : hi; }
     return (sh ? ((lo >> sh) | (hi << (32u - sh))) : lo) & mask;
+}
+// signed geometry: x(s*G) = x((n - s)*G) and only x(Q) leaves the stage, so the smaller of s and n - s is multiplied: it is below
+// 2^255, which keeps the top window's signed digit inside its table (no carry out of bit 255). t: 8 big-endian words, 0 < t < n.
+VG_DEV void vg_tap_fold_scalar(uint32_t t[8]) {
+    uint32_t s[8], m[8];
+    VG_UNROLL for (int i = 0; i < 8; i++) s[i] = t[7 - i];
+    vg_scalar_neg_n(m, s);
+    bool m_less = false, decided = false;
+    VG_UNROLL for (int i = 7; i >= 0; i--) { if (!decided && m[i] != s[i]) { m_less = m[i] < s[i]; decided = true; } }
+    VG_UNROLL for (int i = 0; i < 8; i++) t[7 - i] = m_less ? m[i] : s[i];
 }
 
 // The accumulator of the fast path in XYZZ coordinates (x = X / ZZ, y = Y / ZZZ, ZZ^3 = ZZZ^2): a mixed addition costs 8M + 2S
@@ -174,7 +182,14 @@ VG_DEV bool vg_tap_output_key(fe &qx, fe &qzz, const fe &px, const fe &py, const
     q.x = px; q.y = py; fe_set_one(q.z); q.inf = false;
     bool special = false, affine = true, have = true;        // affine: q.z is still 1
 #endif
-    const uint32_t n_win = vg_tap_windows(bits), mask = (bits >= 32u) ? 0xffffffffu : ((1u << bits) - 1u);
+    const uint32_t n_win = vg_tap_windows(bits);
+    const bool sgn = (bits & VG_TAP_SIGNED) != 0;
+    uint32_t tt[8];
+    VG_UNROLL for (int i = 0; i < 8; i++) tt[i] = t[i];
+#if VG_TAP_SCALAR
+    if (sgn) vg_tap_fold_scalar(tt);            // (the point form cannot flip the sign of t: signed geometries need the scalar form)
+#endif
+    uint32_t carry = 0;
 #ifndef VG_HOST_EMU
     #pragma unroll 1
 #endif
@@ -182,10 +197,18 @@ VG_DEV bool vg_tap_output_key(fe &qx, fe &qzz, const fe &px, const fe &py, const
 #if VG_TAP_SYNC >= 2 && !defined(VG_HOST_EMU)
         if (FAST) __syncthreads();      // every thread of the CTA runs all n_win iterations (inactive ones skip the addition)
 #endif
-        const uint32_t v = vg_tap_digit(t, j, bits);
+        uint32_t off, width; unsigned long long first;
+        vg_tap_window(bits, j, &off, &width, &first);
+        uint32_t v = vg_tap_digit(tt, off, width) + carry;
+        bool neg = false;
+        if (sgn) {                              // digit in [-2^(width-1), 2^(width-1)]: a value above the half borrows from the next window
+            const uint32_t half = 1u << (width - 1u);
+            carry = v > half ? 1u : 0u;
+            if (carry) { v = (1u << width) - v; neg = true; }
+        }
         if (v == 0 || !active || special) continue;
-        VG_ASSERT_AT(viol, j < n_win && v <= mask, 10);
-        const uint32_t *e = tab + ((size_t)j * ((size_t)mask + 1) + v) * 16;
+        VG_ASSERT_AT(viol, j < n_win && v <= (sgn ? (1u << (width - 1u)) : ((1u << width) - 1u)), 10);
+        const uint32_t *e = tab + (size_t)(first + v) * 16;
         fe bx, by;
 #ifdef VG_HOST_EMU
         for (int l = 0; l < 8; l++) { bx.v[l] = e[l]; by.v[l] = e[8 + l]; }
@@ -195,6 +218,7 @@ VG_DEV bool vg_tap_output_key(fe &qx, fe &qzz, const fe &px, const fe &py, const
         bx.v[0] = a0.x; bx.v[1] = a0.y; bx.v[2] = a0.z; bx.v[3] = a0.w; bx.v[4] = a1.x; bx.v[5] = a1.y; bx.v[6] = a1.z; bx.v[7] = a1.w;
         by.v[0] = a2.x; by.v[1] = a2.y; by.v[2] = a2.z; by.v[3] = a2.w; by.v[4] = a3.x; by.v[5] = a3.y; by.v[6] = a3.z; by.v[7] = a3.w;
 #endif
+        if (neg) { fe ny; fe_neg(ny, by); by = ny; }
         if (!have) { q.x = bx; q.y = by; fe_set_one(q.z); q.inf = false; have = true; affine = true; continue; }
         if (FAST) {
 #if VG_TAP_XYZZ

@@ -167,7 +167,7 @@ class GpuRunner:
         return int(self._lib.vgen_cuda_lane_count(self._ctx))
 
     def tap_bits(self):
-        """Window width of the P2TR fixed-base table built so far (0, 16 or 24; see include/vgen_cuda.h)."""
+        """Geometry of the P2TR fixed-base table built so far (0, a window width, or a signed-geometry word; see include/vgen_cuda.h)."""
         return int(self._lib.vgen_cuda_tap_bits(self._ctx))
 
     def launch_count(self):
