@@ -32,9 +32,10 @@ W_INT = {"p2pkh": 3050, "p2wpkh": 3050, "p2sh-p2wpkh": 5425, "p2pkh-uncompressed
          # Ethereum: Keccak-f[1600] on 32-bit halves = 24 x (122 LOP3 + 58 SHF) = 4,320 + walk (both coordinates) ~1,080;
          # ncu counts 5,509 executed per key (profiles/ncu_walk_eth_r01_summary.txt)
          "ethereum": 5400,
-         # P2TR: walk 4.5 field mults + tweak stage A x (8M + 3S) + 4 + 270/64 mults x ~147 slots + one SHA-256 compression,
-         # A = 10 additions with the 26-bit table bench_resident builds (long-job setting; 24 bits: 11, ~21,000; 16 bits: 16, ~29,100)
-         "p2tr": 19400}
+         # P2TR (round 2: output key from the key's scalar, XYZZ accumulator, 9-window signed table that bench_resident builds as the
+         # long-job setting): walk 4.5 field mults + tweak stage 4M+2S, 6 x (8M+2S), 5M+2S over 9 table entries + 4 + 270/64 mults for
+         # the grouped inversion = ~90 field mults x ~147 slots + one SHA-256 compression (round 1, 10 Jacobian additions: 19,400)
+         "p2tr": 14700}
 HBM_BYTES_PER_KEY = 32          # prefix-product scratch: 32 B written + 32 B read per +/- key pair
 # BASELINE config C5: P2PKH address of the key at offset int(0.83 * 2^40) of the window from 2^65 (derived with the oracle by
 # tests/test_full_size_configs.py::test_c5_exact_address_2_40, which fails if this constant is wrong)
