@@ -130,6 +130,28 @@ VG_DEV void vg_tap_fold_scalar(uint32_t t[8]) {
     VG_UNROLL for (int i = 0; i < 8; i++) t[7 - i] = m_less ? m[i] : s[i];
 }
 
+// Table entry of window j for the scalar tt (8 big-endian words): its index in the table, 0 when the digit is 0 (index 0 is the unused
+// zero multiple of window 0). Signed geometries: `carry` runs from window to window, `neg` says the entry's y is to be negated.
+VG_DEV unsigned long long vg_tap_entry(uint32_t g, const uint32_t tt[8], uint32_t j, uint32_t &carry, bool &neg) {
+    uint32_t off, width; unsigned long long first;
+    vg_tap_window(g, j, &off, &width, &first);
+    uint32_t v = vg_tap_digit(tt, off, width) + carry;
+    neg = false;
+    if (g & VG_TAP_SIGNED) {                    // digit in [-2^(width-1), 2^(width-1)]: a value above the half borrows from the next window
+        const uint32_t half = 1u << (width - 1u);
+        carry = v > half ? 1u : 0u;
+        if (carry) { v = (1u << width) - v; neg = true; }
+    }
+    return v ? first + v : 0ull;
+}
+// VG_TAP_PREFETCH = 1: before a key's additions start, all of its table entries are requested into L2 (they are gathered at random
+// from a table of 43 to 112 GB; the additions of the earlier windows would then cover the DRAM latency of the later ones).
+// Measured on B200 (profiles/tap_prefetch_r02.log): 719 against 901 Mkeys/s with the 9-window table, 791 against 856 with the 26-bit
+// one — the stage is not waiting for those loads (16 warps per SM cover them) and the prefetches only add traffic: off.
+#ifndef VG_TAP_PREFETCH
+#define VG_TAP_PREFETCH 0
+#endif
+
 // The accumulator of the fast path in XYZZ coordinates (x = X / ZZ, y = Y / ZZZ, ZZ^3 = ZZZ^2): a mixed addition costs 8M + 2S
 // instead of the Jacobian 8M + 3S, the top window (no Y3, no ZZZ3) 5M + 2S instead of 6M + 3S, and the caller gets ZZ = Z^2, which
 // is what the grouped inversion wants, without a squaring. VG_TAP_XYZZ = 0: Jacobian accumulator.
@@ -184,12 +206,28 @@ VG_DEV bool vg_tap_output_key(fe &qx, fe &qzz, const fe &px, const fe &py, const
 #endif
     const uint32_t n_win = vg_tap_windows(bits);
     const bool sgn = (bits & VG_TAP_SIGNED) != 0;
+    (void)viol;
     uint32_t tt[8];
     VG_UNROLL for (int i = 0; i < 8; i++) tt[i] = t[i];
 #if VG_TAP_SCALAR
     if (sgn) vg_tap_fold_scalar(tt);            // (the point form cannot flip the sign of t: signed geometries need the scalar form)
 #endif
     uint32_t carry = 0;
+#if VG_TAP_PREFETCH && !defined(VG_HOST_EMU)
+    if (FAST && active) {
+        #pragma unroll 1
+        for (uint32_t j = 0; j < n_win; j++) {
+            bool ng;
+            const unsigned long long idx = vg_tap_entry(bits, tt, j, carry, ng);
+            if (idx) {
+                const uint32_t *e = tab + (size_t)idx * 16;
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(e));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(e + 8));
+            }
+        }
+        carry = 0;
+    }
+#endif
 #ifndef VG_HOST_EMU
     #pragma unroll 1
 #endif
@@ -197,18 +235,11 @@ VG_DEV bool vg_tap_output_key(fe &qx, fe &qzz, const fe &px, const fe &py, const
 #if VG_TAP_SYNC >= 2 && !defined(VG_HOST_EMU)
         if (FAST) __syncthreads();      // every thread of the CTA runs all n_win iterations (inactive ones skip the addition)
 #endif
-        uint32_t off, width; unsigned long long first;
-        vg_tap_window(bits, j, &off, &width, &first);
-        uint32_t v = vg_tap_digit(tt, off, width) + carry;
-        bool neg = false;
-        if (sgn) {                              // digit in [-2^(width-1), 2^(width-1)]: a value above the half borrows from the next window
-            const uint32_t half = 1u << (width - 1u);
-            carry = v > half ? 1u : 0u;
-            if (carry) { v = (1u << width) - v; neg = true; }
-        }
-        if (v == 0 || !active || special) continue;
-        VG_ASSERT_AT(viol, j < n_win && v <= (sgn ? (1u << (width - 1u)) : ((1u << width) - 1u)), 10);
-        const uint32_t *e = tab + (size_t)(first + v) * 16;
+        bool neg;
+        const unsigned long long idx = vg_tap_entry(bits, tt, j, carry, neg);
+        if (idx == 0 || !active || special) continue;
+        VG_ASSERT_AT(viol, j < n_win && idx < vg_tap_entries(bits), 10);
+        const uint32_t *e = tab + (size_t)idx * 16;
         fe bx, by;
 #ifdef VG_HOST_EMU
         for (int l = 0; l < 8; l++) { bx.v[l] = e[l]; by.v[l] = e[8 + l]; }
