@@ -389,6 +389,8 @@ def test_multi_device_context_equals_single(runner, devs):
         _check_scan(rm, "p2wpkh", "qq$", 2**64, 1 << 18)
         res = _scan(rm, "p2pkh", ".", 5, 5000)
         assert [int(m.hex, 16) for m in res.matches] == list(range(5, 5005))
+        # P2TR: stage 2 derives every key's scalar from its window's base, whichever lane runs the window
+        _check_scan(rm, "p2tr", "^bc1pq", 2**64 + 99, 1 << 15)
     finally:
         rm.close()
 
