@@ -137,10 +137,11 @@ uint64_t vgen_cuda_window_keys(const vgen_ctx *ctx);
 /* lanes of the context: every GPU is driven through 2 streams (each with its own centres, scratch and hit buffers) whose
  * windows overlap, so that a window's late warps do not leave the SMs under-occupied; lanes = 2 x GPUs */
 int vgen_cuda_lane_count(const vgen_ctx *ctx);
-/* geometry of the P2TR fixed-base table this context has built: 0 none yet; the window width in bits — 16 for short jobs, 24 for
- * jobs of at least 2^30 keys, 26 from 2^36 keys —; or 0x40000000 | n_hi << 8 | W for signed windows (n_hi windows of W + 1 bits, the
- * rest of W bits): 0x4000041c, the 9-window table of 111.7 GB, from 2^38 keys when the device has the room (or what VGEN_TAP_BITS
- * forces: a width, or sW.n_hi); a larger table is kept once built */
+/* geometry of the P2TR fixed-base table this context has built: 0 none yet; a plain window width in bits (only when VGEN_TAP_BITS
+ * forces one, or as the 26-bit fallback); or 0x40000000 | n_hi << 8 | W for signed digits (n_hi windows of W + 1 bits, the rest of
+ * W bits): 0x40000111 (15 windows, 67 MB) for short jobs, 0x40000619 (10 windows, 17 GB) for jobs of at least 2^30 keys, 0x4000041c
+ * (9 windows, 111.7 GB) from 2^36 keys when the device has the room (VGEN_TAP_BITS: a width, or sW.n_hi); a bigger table is kept
+ * once built */
 int vgen_cuda_tap_bits(const vgen_ctx *ctx);
 /* Counters of the context, for tests and run reports: out[0] devices, out[1] devices that have dropped out after a CUDA error
  * (their windows were taken over by the others; VGEN_FAULT_INJECT=<device index>:<n> makes the n-th window issue of a device

@@ -228,21 +228,23 @@ def test_p2tr_exact_address_planted(small_runner):
 
 
 def test_p2tr_long_job_builds_the_wide_table(runner):
-    """A P2TR job of at least 2^32 keys switches the tweak stage to the 24-bit fixed-base table (11 GiB in HBM, 11 additions
-    per key instead of 16; engine.cpp ensure_taproot). Same results as the oracle, through the scan and the digest path."""
+    """A P2TR job of at least 2^30 keys switches the tweak stage from the 15-window table (67 MB) to the 10-window one of signed
+    digits (6 x 26 + 4 x 25 bits, 17 GB in HBM; engine.cpp ensure_taproot). Same results as the oracle, through the scan and the
+    digest path."""
+    MID = 0x40000000 | (6 << 8) | 25
     import os
     start, n = 2**70, (1 << 32) + 12345
     cfg = vg.ScanConfig(format=vg.AddressFormat.P2tr, count=5, start=start, end=start + n - 1)
     res = vg.scan_gpu_with_runner(vg.Pattern("^bc1pqq"), cfg, None, None, runner)
     if "VGEN_TAP_BITS" not in os.environ:
-        assert runner.tap_bits() == 24
+        assert runner.tap_bits() == MID
     keys, _, _ = oracle.scan_range("p2tr", "^bc1pqq", start, 30000)
     assert len(keys) >= 5 and [int(m.hex, 16) for m in res.matches] == keys[:5]
     for m in res.matches:
         assert m.address == oracle.address("p2tr", int(m.hex, 16))[0]
     got = runner.digest_batch("p2tr", start + 777, 3000)          # the wide table stays in place for short calls
     assert got == oracle.digest_batch("p2tr", start + 777, 3000)
-    assert "VGEN_TAP_BITS" in os.environ or runner.tap_bits() == 24
+    assert "VGEN_TAP_BITS" in os.environ or runner.tap_bits() == MID
 
 
 @pytest.mark.parametrize("geom", ["s7.4", "s5.1", "s4.0", "13"])

@@ -241,32 +241,37 @@ bool Engine::upload_dfa(std::string &err) {
     return true;
 }
 
-// Geometry of the P2TR fixed-base table (scan_types.h), chosen per job (measured on B200, profiles/tap_bits_r01.log, tap_signed_r02.log):
-//   16 bits: 16 windows x 65,536 x 64 B = 64 MiB, built in 2 ms; 16 table lookups per key
-//   24 bits: 11 windows x 2^24 x 64 B = 11 GiB of the 180 GB HBM, built in 0.15 s; 11 lookups
-//   26 bits: 10 windows x 2^26 x 64 B = 40 GiB, built in 0.43 s; 10 lookups
-//   signed 4 x 29 + 5 x 28 bits: 9 windows, 1.745 G entries = 111.7 GB; 9 lookups
-// The entries are gathered at random from DRAM either way (ncu: the 64 MiB table is flushed out of L2 by the window's point
-// stream), so a wider table only saves additions. Jobs of >= 2^30 keys take 24 bits, >= 2^36 keys 26 bits, >= 2^38 keys the
-// signed 9-window table (each when the device has the room). VGEN_TAP_BITS forces a geometry: 4..26, or sW.H for the signed
-// one with H windows of W + 1 bits and the rest of W bits (s28.4 is the 9-window table; small ones for tests).
+// Geometry of the P2TR fixed-base table (scan_types.h), chosen per job. Measured on B200 with the round-2 stage
+// (profiles/tap_geometries_r02.log, tap_signed_r02.log; round 1: tap_bits_r01.log), P2TR ^bc1pcat, Mkeys/s:
+//   16 bits            16 windows x 65,536 entries          67 MB   built in 6 ms    564
+//   s17.1 (signed)     15 windows, 1 x 18 + 14 x 17 bits    67 MB            5 ms    587      <- jobs below 2^30 keys
+//   24 bits            11 windows x 2^24                   11.8 GB         0.15 s    787
+//   s25.6 (signed)     10 windows, 6 x 26 + 4 x 25 bits    17.2 GB          0.3 s    840      <- jobs of 2^30 .. 2^36 keys
+//   26 bits            10 windows x 2^26                   42.9 GB         0.45 s    856      (fallback when 112 GB are not free)
+//   s28.4 (signed)      9 windows, 4 x 29 + 5 x 28 bits   111.7 GB          1.2 s    905      <- jobs of at least 2^36 keys
+// The entries are gathered at random from DRAM either way (ncu: even the 64 MiB table is flushed out of L2 by the window's point
+// stream), so a bigger table only saves additions; signed digits halve the entries per window at the price of a conditional
+// negation (2 % at equal window count). VGEN_TAP_BITS forces a geometry: 4..26, or sW.H for the signed one with H windows of
+// W + 1 bits and the rest of W bits.
+static const uint32_t kTapShort = VG_TAP_GEOM_SIGNED(17, 1), kTapMid = VG_TAP_GEOM_SIGNED(25, 6), kTapLong = VG_TAP_GEOM_SIGNED(28, 4);
 static uint32_t tap_bits_for(uint64_t keys_hint) {
     if (const char *e = getenv("VGEN_TAP_BITS")) {
         if (e[0] == 's' || e[0] == 'S') {
             unsigned W = 0, H = 0;
             if (sscanf(e + 1, "%u.%u", &W, &H) >= 1 && W < 256 && H < 256 && vg_tap_geom_valid(VG_TAP_GEOM_SIGNED(W, H))) return VG_TAP_GEOM_SIGNED(W, H);
-            return 16u;
+            return kTapShort;
         }
         long v = strtol(e, nullptr, 10);
         return (uint32_t)(v < 4 ? 4 : v > 26 ? 26 : v);
     }
-    return keys_hint >= (1ull << 38) ? VG_TAP_GEOM_SIGNED(28, 4) : keys_hint >= (1ull << 36) ? 26u : keys_hint >= (1ull << 30) ? 24u : 16u;
+    return keys_hint >= (1ull << 36) ? kTapLong : keys_hint >= (1ull << 30) ? kTapMid : kTapShort;
 }
-static size_t tap_table_bytes(uint32_t geom) { return (size_t)vg_tap_entries(geom) * 64; }
+// a table's size is also its rank: of two geometries the bigger one is the faster one (table above)
+static size_t tap_table_bytes(uint32_t geom) { return geom ? (size_t)vg_tap_entries(geom) * 64 : 0; }
 
 // P2TR needs two more buffers: the stage-1 -> stage-2 point buffer of every lane (64 B per window key) and the fixed-base
-// table of the tweak addition (one per GPU, shared by its lanes). Allocated and built on first use; a wider table replaces
-// a narrower one when a big job comes, never the other way round.
+// table of the tweak stage (one per GPU, shared by its lanes). Allocated and built on first use; a bigger table replaces
+// a smaller one when a big job comes, never the other way round.
 bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
     const Level &F = levels_.back();
     uint32_t want = tap_bits_for(keys_hint);
@@ -275,18 +280,23 @@ bool Engine::ensure_taproot(uint64_t keys_hint, std::string &err) {
         CK(cudaSetDevice(L.device));
         CK(dmalloc((void **)&L.d_points, (size_t)F.window * 64, L.device));
     }
-    if (tap_bits_ != 0 && (tap_bits_ >= want || getenv("VGEN_TAP_BITS"))) return true;
-    for (auto &D : devices_) {            // a big table needs room: fall back to the small one on a crowded device
+    if (tap_bits_ != 0 && (tap_table_bytes(tap_bits_) >= tap_table_bytes(want) || getenv("VGEN_TAP_BITS"))) return true;
+    // a big table needs room: on a crowded device step down to the next smaller one of the list
+    const uint32_t steps[] = {want, 26u, kTapMid, kTapShort};
+    for (auto &D : devices_) {
         if (D.failed) continue;
         size_t free_b = 0, total_b = 0;
         CK(cudaSetDevice(D.device));
         CK(cudaMemGetInfo(&free_b, &total_b));
-        const size_t held = tap_bits_ ? tap_table_bytes(tap_bits_) : 0;      // freed before the new one is allocated
-        if (want > 26 && free_b + held < tap_table_bytes(want) + (8ull << 30)) want = 26;      // > 26: a signed geometry word
-        if (want > 24 && free_b + held < tap_table_bytes(want) + (8ull << 30)) want = 24;
-        if (want > 16 && free_b + held < tap_table_bytes(want) + (4ull << 30)) want = 16;
+        const size_t held = tap_table_bytes(tap_bits_);                       // freed before the new one is allocated
+        for (uint32_t g : steps) {
+            if (tap_table_bytes(g) > tap_table_bytes(want)) continue;
+            want = g;
+            const size_t spare = tap_table_bytes(g) > (1ull << 30) ? (8ull << 30) : (1ull << 30);
+            if (free_b + held >= tap_table_bytes(g) + spare) break;
+        }
     }
-    if (tap_bits_ >= want && tap_bits_ != 0) return true;
+    if (tap_bits_ != 0 && tap_table_bytes(tap_bits_) >= tap_table_bytes(want)) return true;
     const auto t0 = std::chrono::steady_clock::now();
     for (auto &L : lanes_) { if (devices_[L.dev].failed) continue; CK(cudaSetDevice(L.device)); CK(cudaStreamSynchronize(L.stream)); }
     for (auto &D : devices_) {
