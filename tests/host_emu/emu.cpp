@@ -117,6 +117,15 @@ int emu_confirm_eth_fold(const uint32_t *dg, const uint16_t *table, const uint8_
 // fixed-base table (4 keeps the host build cheap).
 static std::vector<uint32_t> g_tap; static uint32_t g_tap_bits = 0;
 int emu_tap_scalar_form() { return VG_TAP_SCALAR; }
+// table geometry (scan_types.h): out = {valid, windows, entries, first bit past the top window}
+void emu_tap_geom(uint32_t g, unsigned long long *out) {
+    out[0] = (unsigned long long)vg_tap_geom_valid(g);
+    if (!out[0]) return;
+    out[1] = vg_tap_windows(g); out[2] = vg_tap_entries(g);
+    uint32_t off, width; unsigned long long first;
+    vg_tap_window(g, (uint32_t)out[1] - 1, &off, &width, &first);
+    out[3] = off + width;
+}
 void emu_scalar_add_mod_n(const uint32_t *a, const uint32_t *b, uint32_t *r) { vg_scalar_add_mod_n(r, a, b); }
 void emu_scalar_neg_n(const uint32_t *k, uint32_t *r) { vg_scalar_neg_n(r, k); }
 void emu_tap_stage2(uint32_t *points, const uint32_t *base8, uint32_t n, uint32_t bits, uint8_t *out32) {

@@ -139,6 +139,26 @@ def test_p2tr_two_stage_vs_oracle(emu):
         assert out.raw == want[:32 * total], start
 
 
+def test_p2tr_table_geometry_words(emu):
+    """scan_types.h: the geometry word of the P2TR fixed-base table — plain widths and signed mixed-radix windows — gives the
+    window count, the table size and windows that cover exactly (signed) or at least (plain) the 256 scalar bits."""
+    SIGNED = 0x40000000
+    out = (C.c_ulonglong * 4)()
+    for b in range(4, 27):
+        emu.emu_tap_geom(b, out)
+        n = (256 + b - 1) // b
+        assert list(out) == [1, n, n << b, n * b]
+    for W, H in [(17, 1), (25, 6), (28, 4), (4, 0), (5, 1), (7, 4), (3, 1), (21, 4)]:
+        emu.emu_tap_geom(SIGNED | (H << 8) | W, out)
+        n = (256 - H) // W
+        assert list(out) == [1, n, H * (2**W + 1) + (n - H) * (2**(W - 1) + 1), 256], (W, H)
+    emu.emu_tap_geom(SIGNED | (4 << 8) | 28, out)
+    assert out[1] == 9 and out[2] == 1_744_830_473 and out[2] * 64 == 111_669_150_272                 # the 9-window table of the longest jobs: 111.7 GB
+    for g in (0, 3, 27, 32, SIGNED | 28, SIGNED | (3 << 8) | 28, SIGNED | (1 << 8) | 2, SIGNED | (1 << 16) | (4 << 8) | 28, SIGNED | (20 << 8) | 31, SIGNED | (16 << 8) | 30):
+        emu.emu_tap_geom(g, out)
+        assert out[0] == 0, hex(g)
+
+
 def test_p2tr_scalar_arithmetic_mod_n(emu):
     """taproot.cuh vg_scalar_add_mod_n / vg_scalar_neg_n (s = t + k or t + n - k mod n): the cases hashing never produces —
     sums that reach n exactly, pass 2^256, or come out 0 — and random operands, against Python integers."""
