@@ -11,9 +11,10 @@
 //           Q = P_even + t*G. The key's scalar k is known (window base + index), and P_even = k*G for even y, (n - k)*G for odd, so
 //           Q = s*G with s = t + k or t + n - k (mod n): ONE fixed-base multiplication, no addition of P (VG_TAP_SCALAR; with it off,
 //           stage 1 stores the even-Y point and stage 2 adds t*G to it: one table addition more per key).
-//           The multiplication runs through a fixed-base table tab[j][v] = v * 2^(bits*j) * G (bits = 16: 16 mixed additions,
-//           64 MiB, L2-resident; bits = 24: 11 additions, 11 GiB of HBM gathered at random), kept in Jacobian form; one field inversion per VG_TAP_GROUP keys (Montgomery's
-//           trick over the group's Z^2) turns X/Z^2 into the 32-byte witness program x(Q), which goes through the
+//           The multiplication runs through a fixed-base table of affine multiples v * 2^(off_j) * G per window j (geometry word:
+//           scan_types.h; signed-digit windows: 15 of them in 67 MB for short jobs, 10 in 17 GB, 9 in 111.7 GB of HBM for the longest,
+//           gathered at random), accumulated in XYZZ coordinates; one field inversion per VG_TAP_GROUP keys (Montgomery's
+//           trick over the group's ZZ = Z^2) turns X/ZZ into the 32-byte witness program x(Q), which goes through the
 //           same matcher as the other formats (interval / exact / Bech32m-fed DFA).
 #pragma once
 #include "match.cuh"
