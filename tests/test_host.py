@@ -339,6 +339,28 @@ def test_product_encoders_vs_oracle_random_and_leading_zeros():
         assert vg.wif_from_key(F.Ethereum, d) == d.hex()
 
 
+def test_product_sha256_portable_and_sha_ni_paths_agree():
+    """host_util.cpp picks the x86 SHA extensions at run time when the CPU has them; VGEN_NO_SHA_NI=1 keeps the portable
+    compression. Both must give the oracle's Base58Check strings (whichever of them this machine runs by default)."""
+    import subprocess
+    import sys
+    code = ("import vgen_b200 as vg\n"
+            "F = vg.AddressFormat\n"
+            "for i in range(64):\n"
+            "    d = bytes((i * 37 + j * 11) & 255 for j in range(32))\n"
+            "    print(vg.address_from_digest(F.P2pkh, d[:20]), vg.address_from_digest(F.P2shP2wpkh, d[:20]), vg.wif_from_key(F.P2pkh, d), vg.wif_from_key(F.P2pkhUncompressed, d))\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for extra in ({}, {"VGEN_NO_SHA_NI": "1"}):
+        env = dict(os.environ, **extra)
+        env.pop("VGEN_NO_SHA_NI", None) if not extra else None
+        outs.append(subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True, check=True).stdout)
+    assert outs[0] == outs[1] and outs[0].count("\n") == 64
+    first = outs[0].splitlines()[0].split()
+    d = bytes((j * 11) & 255 for j in range(32))
+    assert first == [oracle.base58check(b"\x00" + d[:20]), oracle.base58check(b"\x05" + d[:20]), oracle.base58check(b"\x80" + d + b"\x01"), oracle.base58check(b"\x80" + d)]
+
+
 def test_regex_too_big_for_a_device_table_falls_back_to_the_host_nfa(regex_golden):
     """A pattern vgen accepts must not become an error after the swap (src/pattern.rs:21-40 takes whatever `regex` compiles).
     `a.{13}$` needs 2^14 DFA states, more than a device table holds: Pattern still compiles, matches() decides with the NFA, and
